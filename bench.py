@@ -1,0 +1,478 @@
+#!/usr/bin/env python
+"""bench.py — the hot path's headline benchmark on B200.
+
+    python bench.py --gpus N --steps K --warmup W              (N>1: launched by torchrun, one rank per GPU)
+    python bench.py --impl reference --gpus N --steps K --warmup W   (the CPU path on the box's host cores)
+
+Headline workload (BASELINE.json configs[2], the configuration the Mpix/s metric is quoted on; it fits one GPU):
+Mandelbrot 16384 x 16384, 4096 max iterations, view [-2,1] x [-1.5,1.5], through ClNumberCruncher.compute().
+A "step" is one compute() over the whole image.  Three measurements per run:
+  value      Mpix/s with everything resident in HBM (the output stays in the device buffer): CUDA-event time of the
+             device span of each compute(), summed over the K steps, max over ranks.
+  e2e        the same metric through the public API with HOST buffers: every step uploads the view array and downloads
+             the iteration counts into pinned host memory (driver-controlled pipelining hides the download).
+  roofline   achieved FP32 rate of the Mandelbrot kernel = 8 FLOP x (sum of iteration counts) / kernel time, against
+             2 x 128 lanes x SMs x max SM clock (no tensor cores on this path; the bound is the FP32 FMA pipe).
+plus the other BASELINE workloads (streaming SAXPY / vector-add 2^28 floats, n-body 128 Ki bodies) under "workloads",
+each with its own roofline entry, and the CPU oracle timed on a bounded sample ("cpu_baseline").
+Multi-GPU: under torchrun every rank drives one GPU as one device of the split (cekirdekler_b200/spmd.py); the ranks
+exchange only their device times, and the balancer's iterations-to-converge is reported.  The total work is fixed, so
+scaling is "strong".
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import sys
+import threading
+import time
+from pathlib import Path
+
+import numpy as np
+
+ROOT = Path(__file__).resolve().parent
+sys.path.insert(0, str(ROOT))
+
+METRIC = "mandelbrot_mpix_per_s"
+UNIT = "Mpix/s"
+W = H = 16384
+MAX_ITER = 4096
+E = 4  # pixels per work-item of the `mandelbrot` kernel
+
+
+def peaks():
+    p = {"hbm_gbs": 6650.0, "sm_max_mhz": 1965.0, "source": "fallback (B200_PROFILING.md)"}
+    f = ROOT / "MEASURED_PEAKS.json"
+    if f.exists():
+        try:
+            j = json.loads(f.read_text())
+            p.update(hbm_gbs=float(j["hbm_gbs"]), sm_max_mhz=float(j["sm_max_mhz"]), source="MEASURED_PEAKS.json")
+        except Exception:
+            pass
+    return p
+
+
+class ClockSampler:
+    """Samples SM clock and throttle reasons through NVML while the timed region runs."""
+
+    def __init__(self, index: int):
+        self.index, self.samples, self.reasons, self.max_mhz = index, [], set(), None
+        self._stop = threading.Event()
+        self._t = None
+        try:
+            import pynvml
+
+            pynvml.nvmlInit()
+            self.nv = pynvml
+            self.h = pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.max_mhz = pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM)
+        except Exception:
+            self.nv = None
+
+    def _run(self):
+        nv = self.nv
+        names = {
+            nv.nvmlClocksThrottleReasonHwSlowdown: "hw_slowdown",
+            nv.nvmlClocksThrottleReasonHwThermalSlowdown: "hw_thermal_slowdown",
+            nv.nvmlClocksThrottleReasonSwThermalSlowdown: "sw_thermal_slowdown",
+            nv.nvmlClocksThrottleReasonSwPowerCap: "sw_power_cap",
+        }
+        while not self._stop.is_set():
+            try:
+                self.samples.append(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM))
+                r = nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
+                for bit, name in names.items():
+                    if r & bit:
+                        self.reasons.add(name)
+            except Exception:
+                pass
+            self._stop.wait(0.05)
+
+    def __enter__(self):
+        if self.nv:
+            self._t = threading.Thread(target=self._run, daemon=True)
+            self._t.start()
+        return self
+
+    def __exit__(self, *a):
+        self._stop.set()
+        if self._t:
+            self._t.join()
+
+    def summary(self):
+        if not self.samples:
+            return {"sm_mhz": None, "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons)}
+        return {"sm_mhz": float(np.median(self.samples)), "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons)}
+
+
+def dist_env():
+    return int(os.environ.get("RANK", "0")), int(os.environ.get("WORLD_SIZE", "1")), int(os.environ.get("LOCAL_RANK", "0"))
+
+
+# ------------------------------------------------------------------------------------------------ CPU arm
+def cpu_sample(po, view, seconds_target=12.0):
+    """Times the oracle (all host threads) on a strided sample of the C3 image sized for ~seconds_target.
+    The stride is odd, hence coprime with the 2^14-pixel row length: the sample walks over every column and row band
+    and sees the image's cost distribution (a probe with the same property calibrates the sample size)."""
+    npix = W * H
+    probe_stride, probe = 4099, 1 << 15
+    t0 = time.perf_counter()
+    po.mandelbrot_sample(view, 777, probe_stride, probe)
+    pix_per_s = probe / max(time.perf_counter() - t0, 1e-3)
+    count = int(max(probe, min(npix // 3, pix_per_s * seconds_target)))
+    stride = max(3, (npix - 1000) // count) | 1
+    buf = np.zeros(count, np.int32)
+    t0 = time.perf_counter()
+    iters = po.mandelbrot_sample(view, 777, stride, count, buf)
+    dt = time.perf_counter() - t0
+    return {"pixels": count, "seconds": dt, "iters": int(iters), "stride": stride, "offset": 777, "values": buf}
+
+
+def run_reference(args):
+    rank, world, _ = dist_env()
+    if rank != 0:
+        return
+    from oracle import pyoracle as po
+
+    view = po.mandelbrot_view(W, H, MAX_ITER)
+    per_step = max(2.0, min(20.0, 90.0 / max(1, args.steps + args.warmup)))
+    for _ in range(args.warmup):
+        cpu_sample(po, view, per_step / 4)
+    tot_pix, tot_s = 0, 0.0
+    for _ in range(args.steps):
+        s = cpu_sample(po, view, per_step)
+        tot_pix += s["pixels"]
+        tot_s += s["seconds"]
+    v = tot_pix / tot_s / 1e6
+    line = {
+        "impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": tot_s / args.steps * 1e3, "higher_is_better": True, "scaling": "strong",
+        "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": f"mandelbrot {W}x{H} maxIter {MAX_ITER} view [-2,1]x[-1.5,1.5] (BASELINE configs[2])",
+                   "note": "the reference's PoCL/C# path cannot run on this box (no CLR, no OpenCL); this is the CPU "
+                           "restatement oracle/oracle.cpp on all host threads"},
+        "cpu_baseline": {"value": v, "unit": UNIT, "cores": po.threads(), "kind": "port",
+                         "sample": f"{tot_pix // args.steps} pixels per step, an odd-strided sample across the whole {W}x{H} image"},
+        "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line))
+
+
+# ------------------------------------------------------------------------------------------------ GPU arm helpers
+def first_stable(imb, tol=1.05, hold=3):
+    for k in range(len(imb) - hold):
+        if all(v <= tol for v in imb[k:k + hold + 1]):
+            return k + 1
+    return None
+
+
+def bench_saxpy(ck, kernels, dev, shim, pk, steps, warmup):
+    """C2: streaming SAXPY, 2^28 floats, 16 blobs: resident (HBM roofline) and streamed (host-link roofline)."""
+    n = 1 << 28
+    cr = ck.ClNumberCruncher(dev, kernels.source("stream"))
+    assert cr.errorCode() == 0, cr.errorMessage()
+    alpha, x, y = ck.ClFloatArray(1), ck.ClFloatArray(n), ck.ClFloatArray(n)
+    alpha[0] = 2.0
+    x.view[:] = 3.0
+    y.view[:] = (np.arange(n, dtype=np.int64) % (1 << 20)).astype(np.float32)
+    y0 = y.view[:4096].copy()
+    alpha.readOnly = True
+    for a in (x, y):
+        a.partialRead, a.read = True, False
+        a.numberOfElementsPerWorkItem = 4
+    x.readOnly = True
+    out = {}
+    g = alpha.nextParam(x, y)
+    # streamed: both pipeline modes, host buffers every call
+    for mode, ptype in (("event", ck.PIPELINE_EVENT), ("driver", ck.PIPELINE_DRIVER)):
+        ts = []
+        for i in range(warmup + steps):
+            t0 = time.perf_counter()
+            assert g.compute(cr, 10 + int(ptype), "saxpy4", n // 4, 256, 0, True, ptype, 16) == 0
+            if i >= warmup:
+                ts.append(time.perf_counter() - t0)
+        dt = float(np.mean(ts))
+        out[f"streamed_{mode}"] = {"ms_per_step": dt * 1e3, "GBps_algorithmic": 12.0 * n / dt / 1e9,
+                                   "h2d_GBps": 8.0 * n / dt / 1e9, "d2h_GBps": 4.0 * n / dt / 1e9}
+    calls = 2 * (warmup + steps)
+    exp = (y0 + np.float32(6.0) * calls).astype(np.float32)   # exact: small integers
+    out["parity_head_exact"] = bool(np.array_equal(y.view[:4096], exp))
+    # resident: flags cleared after the first call (as Kamera.cs:271-272 does) → no transfers, kernel only
+    g_res = alpha.nextParam(x, y)
+    rw = ["", "", ""]
+    ts = []
+    for i in range(max(3, warmup) + steps):
+        assert g_res.compute(cr, 20, "saxpy4", n // 4, 256, 0, False, True, 4, readWritesReady=rw, elementsPerItemReady=[1, 4, 4]) == 0
+        if i >= max(3, warmup):
+            ts.append(cr.benchmarks(20)[0] * 1e-3)
+    dt = float(np.mean(ts))
+    gbs = 12.0 * n / dt / 1e9
+    out["resident"] = {"ms_per_step": dt * 1e3, "GBps": gbs,
+                       "roofline": {"bound": "hbm", "achieved": gbs, "peak": pk["hbm_gbs"], "unit": "GB/s", "frac": gbs / pk["hbm_gbs"],
+                                    "traffic": None, "peak_source": pk["source"]}}
+    for a in (alpha, x, y):
+        a.dispose()
+    cr.dispose()
+    return out
+
+
+def bench_nbody(ck, kernels, po, devs, pk, sms, steps, warmup, spmd_attach=None):
+    """C4: all-pairs n-body, 128 Ki bodies float4; pos is a whole-array read, vel/posOut are sliced."""
+    n = 131072
+    cr = ck.ClNumberCruncher(devs, kernels.source("nbody"))
+    assert cr.errorCode() == 0, cr.errorMessage()
+    if spmd_attach:
+        spmd_attach(cr)
+    pos = np.zeros((n, 4), np.float32)
+    for c in range(3):
+        pos[:, c] = po.uniform(0xC0FFEE + c, n, -15, 15)
+    pos[:, 3] = 1.0
+    pa, pb, vel, params = ck.ClFloatArray(4 * n), ck.ClFloatArray(4 * n), ck.ClFloatArray(4 * n), ck.ClFloatArray(4)
+    pa.view[:] = pos.reshape(-1)
+    params.view[:] = [1e-3, 1e-4, n, 0]
+    params.readOnly = True
+    vel.partialRead, vel.read = True, False
+    for a in (pa, pb, vel):
+        a.numberOfElementsPerWorkItem = 4
+    src, dst = pa, pb
+    ts_wall, ts_dev = [], []
+    for i in range(warmup + steps):
+        src.read, src.partialRead, src.write = True, False, False
+        dst.read, dst.partialRead, dst.write = False, False, True
+        t0 = time.perf_counter()
+        assert src.nextParam(vel, dst, params).compute(cr, 1, "nBody3D", n, 256) == 0
+        if i >= warmup:
+            ts_wall.append(time.perf_counter() - t0)
+            ts_dev.append(max(cr.benchmarks(1)) * 1e-3)
+        src, dst = dst, src
+    dt_dev, dt_wall = float(np.mean(ts_dev)), float(np.mean(ts_wall))
+    inter = float(n) * n
+    peak = 2.0 * 128 * sms * pk["sm_max_mhz"] * 1e6 / 1e12
+    ach = 20.0 * inter / dt_dev / 1e12
+    res = {"bodies": n, "ms_per_step_device": dt_dev * 1e3, "ms_per_step_e2e": dt_wall * 1e3,
+           "GInter_per_s": inter / dt_dev / 1e9, "GInter_per_s_e2e": inter / dt_wall / 1e9,
+           "roofline": {"bound": "fp32", "achieved": ach, "peak": peak, "unit": "TFLOP/s", "frac": ach / peak, "traffic": None,
+                        "note": "20 FLOP per interaction; device span includes the 2 MiB position upload and slice transfers"}}
+    for a in (pa, pb, vel, params):
+        a.dispose()
+    cr.dispose()
+    return res
+
+
+# ------------------------------------------------------------------------------------------------ GPU arm
+def run_ours(args):
+    rank, world, local = dist_env()
+    import cekirdekler_b200 as ck
+    from cekirdekler_b200 import kernels, spmd
+    from cekirdekler_b200._native import host, shim
+    from oracle import pyoracle as po  # checker + cpu_baseline leg only
+
+    L = shim()
+    if L.ckDeviceCount() <= 0:
+        raise SystemExit("bench.py: no CUDA device visible; there is no CPU fallback (use --impl reference for the CPU arm)")
+    pk = peaks()
+    spmd_mode = world > 1
+    if spmd_mode:
+        spmd.init_process_group_from_env()
+        import torch
+        import torch.distributed as dist
+
+        torch_dev = torch.device("cuda", local)
+        devs = ck.ClDevices([local])
+        n_gpus = world
+    else:
+        dist = None
+        n_gpus = max(1, args.gpus)
+        avail = L.ckDeviceCount()
+        if n_gpus > avail:
+            raise SystemExit(f"bench.py: --gpus {n_gpus} but only {avail} visible")
+        devs = ck.ClDevices(list(range(n_gpus)))
+    sms = host().ckh_gpu_compute_units(devs.ordinals[0])
+
+    def barrier():
+        if spmd_mode:
+            dist.barrier()
+
+    def allmax(v: float) -> float:
+        if not spmd_mode:
+            return v
+        t = torch.tensor([v], dtype=torch.float64, device=torch_dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    def allsum(v: float) -> float:
+        if not spmd_mode:
+            return v
+        t = torch.tensor([v], dtype=torch.float64, device=torch_dev)
+        dist.all_reduce(t, op=dist.ReduceOp.SUM)
+        return float(t.item())
+
+    cr = ck.ClNumberCruncher(devs, kernels.source("mandelbrot"))
+    assert cr.errorCode() == 0, cr.errorMessage()
+    cr.balancerMode = 1 if args.balancer == "adaptive" else 0
+    if spmd_mode:
+        spmd.attach(cr, rank, world, torch_dev)
+    npix = W * H
+    view = ck.ClArray(8, np.float32)
+    view.view[:] = po.mandelbrot_view(W, H, MAX_ITER)
+    view.readOnly = True
+    out = ck.ClArray(npix, np.int32)   # pinned host array, 1 GiB; every rank writes only its own slice
+    out.writeOnly = True
+    out.numberOfElementsPerWorkItem = E
+    items = npix // E
+
+    def my_slices(cid):
+        r, f = cr.globalRanges(cid), cr.globalReferences(cid)
+        idx = [rank] if spmd_mode else range(len(r))
+        return [(f[i] * E, r[i] * E) for i in idx]
+
+    # ---- leg 1: device-resident (value + roofline): no download, kernel span timed with CUDA events in the shim ----
+    CID_RES = 1
+    rw_res = [" read  ro ", ""]           # view: 32-byte upload; out: stays in HBM
+    g = view.nextParam(out)
+    shares, imbalance = [], []
+
+    def step_resident():
+        assert g.compute(cr, CID_RES, "mandelbrot", items, 256, 0, False, True, 4, readWritesReady=rw_res, elementsPerItemReady=[1, E]) == 0
+        t_local = cr.benchmarks(CID_RES)
+        return t_local
+
+    for _ in range(args.warmup):
+        t = step_resident()
+        tt = cr_times(cr, CID_RES, t, spmd_mode, allgather=(lambda v: gather(dist, torch, torch_dev, v, world)) if spmd_mode else None)
+        shares.append(cr.globalRanges(CID_RES))
+        imbalance.append(max(tt) / (sum(tt) / len(tt)))
+    barrier()
+    cr.sync()
+    launches0 = L.ckLaunchCount()
+    dev_ms = 0.0
+    with ClockSampler(devs.ordinals[0]) as clocks:
+        t0 = time.perf_counter()
+        for _ in range(args.steps):
+            t = step_resident()
+            tt = cr_times(cr, CID_RES, t, spmd_mode, allgather=(lambda v: gather(dist, torch, torch_dev, v, world)) if spmd_mode else None)
+            dev_ms += max(tt)                  # devices run concurrently: the step takes as long as its slowest device
+            shares.append(cr.globalRanges(CID_RES))
+            imbalance.append(max(tt) / (sum(tt) / len(tt)))
+        cr.sync()
+        barrier()
+        wall = time.perf_counter() - t0
+    launches = L.ckLaunchCount() - launches0
+    dev_ms = allmax(dev_ms)
+    wall = allmax(wall)
+    launches = int(allsum(float(launches)))
+    ms_per_step = dev_ms / args.steps
+    value = npix / (ms_per_step * 1e-3) / 1e6
+
+    # ---- leg 2: end to end through the public API with host buffers (view upload + slice download every step) ----
+    CID_E2E = CID_RES   # same compute id: the balanced split carries over from the resident leg
+    e2e_t = []
+    for i in range(args.warmup + args.steps):
+        barrier()
+        t0 = time.perf_counter()
+        assert g.compute(cr, CID_E2E, "mandelbrot", items, 256, 0, True, ck.PIPELINE_DRIVER, 16) == 0
+        dt = allmax(time.perf_counter() - t0)
+        if i >= args.warmup:
+            e2e_t.append(dt)
+    e2e_ms = float(np.mean(e2e_t)) * 1e3
+    e2e_value = npix / (e2e_ms * 1e-3) / 1e6
+
+    # ---- work accounting and in-run parity on the oracle's strided sample ----
+    local_iters = 0
+    for (p0, cnt) in my_slices(CID_E2E):
+        local_iters += int(out.view[p0:p0 + cnt].sum(dtype=np.int64))
+    total_iters = allsum(float(local_iters))
+    line_cpu, parity = None, None
+    if rank == 0:
+        s = cpu_sample(po, view.view, 12.0)
+        idx = s["offset"] + s["stride"] * np.arange(s["pixels"], dtype=np.int64)
+        mine = np.zeros(npix, bool)
+        for (p0, cnt) in my_slices(CID_E2E):
+            mine[p0:p0 + cnt] = True
+        sel = mine[idx]
+        parity = {"sample_pixels_checked": int(sel.sum()), "mismatches": int((out.view[idx[sel]] != s["values"][sel]).sum())}
+        line_cpu = {"value": s["pixels"] / s["seconds"] / 1e6, "unit": UNIT, "cores": po.threads(), "kind": "port",
+                    "sample": f"{s['pixels']} pixels (every {s['stride']}th of the {W}x{H} image), {s['iters']} iterations, {s['seconds']:.1f} s"}
+
+    flops = 8.0 * total_iters
+    peak_tf = 2.0 * 128 * sms * pk["sm_max_mhz"] * 1e6 / 1e12
+    kernel_s = dev_ms / args.steps * 1e-3      # resident leg: the span is the kernel (+ a 32-byte upload)
+    ach = flops / n_gpus / kernel_s / 1e12     # per-GPU rate (each GPU runs its share concurrently)
+    clk = clocks.summary()
+    roof = {"bound": "fp32", "achieved": ach, "peak": peak_tf, "unit": "TFLOP/s", "frac": ach / peak_tf, "traffic": None,
+            "kernel": "mandelbrot", "per_gpu": True,
+            "algorithmic": f"8 FLOP x {int(total_iters)} executed iterations (sum of the output counts, bit-exact with the oracle)",
+            "peak_source": f"2 x 128 lanes x {sms} SMs x {pk['sm_max_mhz']:.0f} MHz ({pk['source']}); no tensor cores on this path",
+            "frac_at_observed_clock": (ach / (2.0 * 128 * sms * clk["sm_mhz"] * 1e6 / 1e12)) if clk.get("sm_mhz") else None}
+
+    workloads = {}
+    if args.all and rank == 0 and not spmd_mode:
+        workloads["saxpy_c2"] = bench_saxpy(ck, kernels, devs[0], L, pk, max(2, args.steps // 2), 1)
+    if args.all:
+        attach = (lambda c: spmd.attach(c, rank, world, torch_dev)) if spmd_mode else None
+        nb = bench_nbody(ck, kernels, po, devs, pk, sms, max(3, args.steps), 2, attach)
+        workloads["nbody_c4"] = nb
+
+    if rank == 0:
+        line = {
+            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": n_gpus, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
+            "dtype": "f32", "data": "synthetic",
+            "config": {"workload": f"mandelbrot {W}x{H} maxIter {MAX_ITER} view [-2,1]x[-1.5,1.5] (BASELINE configs[2]), "
+                                   f"{E} pixels per work-item, local 256, via ClNumberCruncher.compute",
+                       "parallelism": ("spmd one process per GPU" if spmd_mode else "one process") + f" x{n_gpus}",
+                       "l2": "output 1 GiB per step >> 126 MB L2, no reuse between steps",
+                       "balancer": args.balancer},
+            "wall_ms_per_step": wall / args.steps * 1e3,
+            "clocks": clk,
+            "e2e": {"value": e2e_value, "unit": UNIT, "ms_per_step": e2e_ms, "h2d_bytes_per_step": 32 * n_gpus,
+                    "d2h_bytes_per_step": 4 * npix, "mode": "driver-controlled pipeline, 16 blobs, pinned host arrays"},
+            "gpu_launches": launches,
+            "roofline": roof,
+            "cpu_baseline": line_cpu,
+            "parity": parity,
+            "balancer": {"iterations_to_converge": first_stable(imbalance) if n_gpus > 1 else 0,
+                         "imbalance_max_over_mean": [round(v, 4) for v in imbalance],
+                         "final_shares": [round(x / items, 4) for x in shares[-1]] if shares else None},
+            "workloads": workloads,
+        }
+        print(json.dumps(line))
+    if spmd_mode:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+def gather(dist, torch, dev, v: float, world: int):
+    mine = torch.tensor([v], dtype=torch.float64, device=dev)
+    outt = torch.empty(world, dtype=torch.float64, device=dev)
+    dist.all_gather_into_tensor(outt, mine)
+    return outt.cpu().tolist()
+
+
+def cr_times(cr, cid, local_times, spmd_mode, allgather=None):
+    """Per-device times of the last call over ALL devices of the split."""
+    if not spmd_mode:
+        return [max(t, 1e-9) for t in local_times]
+    return [max(t, 1e-9) for t in allgather(local_times[0])]
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--balancer", default="adaptive", choices=["adaptive", "reference"])
+    ap.add_argument("--no-all", dest="all", action="store_false", help="skip the SAXPY and n-body workloads")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_ours(args)
+
+
+if __name__ == "__main__":
+    main()

@@ -1,0 +1,105 @@
+// mandelbrot.cu — K1 of the hot path: escape-time Mandelbrot, FP32-FMA-bound.
+//
+// The reference tree has no Mandelbrot source (its mandelbrot_bench ships only as a binary: SURVEY.md F4), so the
+// arithmetic is defined here and, identically, in oracle/oracle.cpp::oracle_mandelbrot:
+//   view = { x0, y0, dx, dy, (float)W, (float)maxIter, -, - }      (scalars travel in a small `read` array: F9)
+//   pixel p: px = p % W, py = p / W, cx = fma(px, dx, x0), cy = fma(py, dy, y0), z0 = 0
+//   out[p] = first k in [0, maxIter) with fma(x_k, x_k, y_k*y_k) > 4, else maxIter
+//   x_{k+1} = fma(x_k, x_k, cx - y_k*y_k),  y_{k+1} = fma(x_k + x_k, y_k, cy)
+// Every operation is an explicit round-to-nearest intrinsic, so the compiler can neither fuse nor reorder them and the
+// iteration counts are bit-identical to the CPU oracle.
+//
+// Launch contract (ClNumberCruncher): one work-item = MANDEL_E consecutive pixels (`numberOfElementsPerWorkItem = 4`
+// on the output array), so a 256-thread work-group owns 1024 consecutive pixels and a device's share is a contiguous
+// pixel range starting at get_global_id-derived offsets.  Each lane stores its 4 counts with one 16-byte store.
+//
+// Roofline: 5 FMA-pipe operations per iteration (FMUL, FADD, FADD, FFMA, FFMA).  The escape test is hoisted out of the
+// inner loop: MANDEL_K iterations run unchecked, then one test; if the orbit left the radius-2 disc inside the block,
+// the block is replayed from its saved start with a per-iteration test to find the exact count.  That is exact because
+// for |c|^2 <= 3.9 an orbit that has left the disc keeps growing (|z'| >= |z|^2 - |c| >= 1.05 |z| once |z| > 2 - 3e-7,
+// far above float rounding error) until it overflows to inf/NaN, and !(m <= 4) catches all three; pixels with
+// |c|^2 > 3.9 (a thin ring that escapes within a few iterations, plus the needle tip near c = -2) take the
+// per-iteration path from the start.  Work is counted as 8 FLOP per executed iteration, so the
+// instruction-issue ceiling of this formulation is 8 / (2 * (5 + overhead)) of the FFMA peak.
+
+#define MANDEL_E 4
+#define MANDEL_K 16
+
+// exact per-iteration loop: at most `limit` iterations from state (x, y); returns the number executed before escape
+__device__ __forceinline__ int mandel_exact(float& x, float& y, const float cx, const float cy, const int limit)
+{
+    int k = 0;
+    while (k < limit) {
+        const float yy = __fmul_rn(y, y);
+        const float m = __fmaf_rn(x, x, yy);
+        if (m > 4.0f) break;
+        const float t = __fsub_rn(cx, yy);
+        const float x2 = __fadd_rn(x, x);
+        y = __fmaf_rn(x2, y, cy);
+        x = __fmaf_rn(x, x, t);
+        k++;
+    }
+    return k;
+}
+
+__device__ __forceinline__ int mandel_pixel(const float cx, const float cy, const int maxIter)
+{
+    float x = 0.0f, y = 0.0f;
+    int n = 0;
+    const float c2 = __fmaf_rn(cx, cx, __fmul_rn(cy, cy));
+    if (c2 <= 3.9f) {
+        // blocks of MANDEL_K unchecked iterations
+        while (n + MANDEL_K <= maxIter) {
+            const float xs = x, ys = y;
+#pragma unroll
+            for (int u = 0; u < MANDEL_K; u++) {
+                const float yy = __fmul_rn(y, y);
+                const float t = __fsub_rn(cx, yy);
+                const float x2 = __fadd_rn(x, x);
+                y = __fmaf_rn(x2, y, cy);
+                x = __fmaf_rn(x, x, t);
+            }
+            const float m = __fmaf_rn(x, x, __fmul_rn(y, y));
+            if (!(m <= 4.0f)) {
+                // left the disc somewhere in (n, n + K]: replay this block with the exact test.  The test at the
+                // block's last state is included, so the replay may run all K iterations (escape exactly at n + K).
+                x = xs;
+                y = ys;
+                return n + mandel_exact(x, y, cx, cy, MANDEL_K);
+            }
+            n += MANDEL_K;
+        }
+    }
+    return n + mandel_exact(x, y, cx, cy, maxIter - n);
+}
+
+__kernel void mandelbrot(const float* __restrict__ view, int* __restrict__ out)
+{
+    const float x0 = __ldg(view + 0), y0 = __ldg(view + 1), dx = __ldg(view + 2), dy = __ldg(view + 3);
+    const unsigned int W = (unsigned int)__ldg(view + 4);
+    const int maxIter = (int)__ldg(view + 5);
+
+    const unsigned int item = (unsigned int)get_global_id(0);
+    const unsigned int p0 = item * MANDEL_E;  // first pixel of this work-item; W*H <= 2^31 (C# int ranges, F10)
+    int r[MANDEL_E];
+#pragma unroll
+    for (int e = 0; e < MANDEL_E; e++) {
+        const unsigned int p = p0 + e;
+        const unsigned int py = p / W, px = p - py * W;
+        const float cx = __fmaf_rn((float)px, dx, x0);
+        const float cy = __fmaf_rn((float)py, dy, y0);
+        r[e] = mandel_pixel(cx, cy, maxIter);
+    }
+    *reinterpret_cast<int4*>(out + p0) = make_int4(r[0], r[1], r[2], r[3]);
+}
+
+// 1 pixel per work-item variant (numberOfElementsPerWorkItem = 1), for callers that want the plain mapping
+__kernel void mandelbrot1(const float* __restrict__ view, int* __restrict__ out)
+{
+    const float x0 = __ldg(view + 0), y0 = __ldg(view + 1), dx = __ldg(view + 2), dy = __ldg(view + 3);
+    const unsigned int W = (unsigned int)__ldg(view + 4);
+    const int maxIter = (int)__ldg(view + 5);
+    const unsigned int p = (unsigned int)get_global_id(0);
+    const unsigned int py = p / W, px = p - py * W;
+    out[p] = mandel_pixel(__fmaf_rn((float)px, dx, x0), __fmaf_rn((float)py, dy, y0), maxIter);
+}

@@ -1,0 +1,236 @@
+// program.cpp — kernel-source front-end of libKutuphaneCL.so: source rewrite + NVRTC → sm_100a cubin.
+//
+// Replaces the clBuildProgram step behind createProgram (reference: ClProgram.cs:64-67 called from
+// Worker.cs:261-272).  The reference passes the user's kernel string unmodified to the OpenCL device
+// compiler; here the string is (1) rewritten so that every `__kernel void f(args)` / `kernel void f(args)`
+// (the spellings ClNumberCruncher's regex recognises, ClNumberCruncher.cs:219-228) becomes
+// `extern "C" __global__ void f(const unsigned int __ck_goff, args)`, (2) prefixed with ck_prelude.cuh and
+// (3) compiled by NVRTC straight to a cubin for the device's architecture (sm_100a on B200).
+// Compiled images are cached per (source, arch) so that the N workers of one cruncher compile once.
+#include "handles.h"
+
+#include <nvrtc.h>
+
+#include <cctype>
+#include <cstring>
+#include <map>
+#include <sstream>
+
+namespace ck {
+
+static const char* kPrelude =
+#include "ck_prelude_embed.inc"
+    ;
+
+static bool ident_char(char c) { return std::isalnum((unsigned char)c) || c == '_'; }
+
+// Finds `kernel void name(` / `__kernel void name(` occurrences outside comments and rewrites them.
+std::string rewrite_kernels(const std::string& src, std::vector<std::pair<std::string, int>>* kernels_out) {
+    std::string out;
+    out.reserve(src.size() + 256);
+    const size_t n = src.size();
+    size_t i = 0;
+    while (i < n) {
+        // copy comments and string literals verbatim
+        if (src[i] == '/' && i + 1 < n && src[i + 1] == '/') {
+            size_t e = src.find('\n', i);
+            if (e == std::string::npos) e = n;
+            out.append(src, i, e - i);
+            i = e;
+            continue;
+        }
+        if (src[i] == '/' && i + 1 < n && src[i + 1] == '*') {
+            size_t e = src.find("*/", i + 2);
+            e = (e == std::string::npos) ? n : e + 2;
+            out.append(src, i, e - i);
+            i = e;
+            continue;
+        }
+        if (src[i] == '"') {
+            size_t e = i + 1;
+            while (e < n && src[e] != '"') e += (src[e] == '\\') ? 2 : 1;
+            e = (e < n) ? e + 1 : n;
+            out.append(src, i, e - i);
+            i = e;
+            continue;
+        }
+        // candidate token start?
+        bool at_token_start = (i == 0) || !ident_char(src[i - 1]);
+        size_t tok = 0;
+        if (at_token_start) {
+            if (src.compare(i, 8, "__kernel") == 0 && (i + 8 >= n || !ident_char(src[i + 8]))) tok = 8;
+            else if (src.compare(i, 6, "kernel") == 0 && (i + 6 >= n || !ident_char(src[i + 6]))) tok = 6;
+        }
+        if (!tok) {
+            out.push_back(src[i++]);
+            continue;
+        }
+        // kernel \s+ void \s+ name \s* (
+        size_t p = i + tok;
+        size_t q = p;
+        while (q < n && std::isspace((unsigned char)src[q])) q++;
+        if (q == p || src.compare(q, 4, "void") != 0 || (q + 4 < n && ident_char(src[q + 4]))) {
+            out.append(src, i, tok);
+            i += tok;
+            continue;
+        }
+        size_t r = q + 4;
+        size_t r0 = r;
+        while (r < n && std::isspace((unsigned char)src[r])) r++;
+        size_t name_b = r;
+        while (r < n && ident_char(src[r])) r++;
+        size_t name_e = r;
+        while (r < n && std::isspace((unsigned char)src[r])) r++;
+        if (r0 == name_b || name_e == name_b || r >= n || src[r] != '(') {
+            out.append(src, i, tok);
+            i += tok;
+            continue;
+        }
+        // matching ')'
+        size_t depth = 0, close = std::string::npos;
+        for (size_t k = r; k < n; k++) {
+            if (src[k] == '(') depth++;
+            else if (src[k] == ')') {
+                if (--depth == 0) { close = k; break; }
+            }
+        }
+        if (close == std::string::npos) {
+            out.append(src, i, tok);
+            i += tok;
+            continue;
+        }
+        std::string name = src.substr(name_b, name_e - name_b);
+        std::string params = src.substr(r + 1, close - r - 1);
+        // count parameters (commas at depth 0); "(void)" and "()" mean none
+        std::string trimmed;
+        for (char c : params) if (!std::isspace((unsigned char)c)) trimmed.push_back(c);
+        int count = 0;
+        if (!trimmed.empty() && trimmed != "void") {
+            count = 1;
+            int d = 0;
+            for (char c : params) {
+                if (c == '(' || c == '[' || c == '<') d++;
+                else if (c == ')' || c == ']' || c == '>') d--;
+                else if (c == ',' && d == 0) count++;
+            }
+        }
+        out += "extern \"C\" __global__ void ";
+        out += name;
+        out += "(const unsigned int __ck_goff";
+        if (count > 0) {
+            out += ", ";
+            out += params;
+        }
+        out += ")";
+        if (kernels_out) kernels_out->emplace_back(name, count);
+        i = close + 1;
+    }
+    return out;
+}
+
+// `// ck-nvrtc: <option> <option>` lines let a kernel string choose compiler flags (the reference API has
+// no other channel than the source text: F9 in SURVEY.md).
+static void collect_options(const std::string& src, std::vector<std::string>* opts) {
+    const std::string key = "ck-nvrtc:";
+    size_t pos = 0;
+    while ((pos = src.find(key, pos)) != std::string::npos) {
+        size_t e = src.find('\n', pos);
+        if (e == std::string::npos) e = src.size();
+        std::istringstream is(src.substr(pos + key.size(), e - pos - key.size()));
+        std::string o;
+        while (is >> o) opts->push_back(o);
+        pos = e;
+    }
+}
+
+static std::mutex g_cache_mu;
+static std::map<std::string, std::shared_ptr<Cubin>> g_cache;
+
+std::shared_ptr<Cubin> compile_source(const std::string& user_src, int cc_major, int cc_minor) {
+    char arch[64];
+    // family-specific ("a") targets exist from sm_90 on; B200 is 10.0 → sm_100a
+    snprintf(arch, sizeof arch, "--gpu-architecture=sm_%d%d%s", cc_major, cc_minor, cc_major >= 9 ? "a" : "");
+    std::string key = std::string(arch) + "\n" + user_src;
+    {
+        std::lock_guard<std::mutex> lk(g_cache_mu);
+        auto it = g_cache.find(key);
+        if (it != g_cache.end()) return it->second;
+    }
+    auto cb = std::make_shared<Cubin>();
+    std::string body = rewrite_kernels(user_src, &cb->kernels);
+    std::string full = std::string(kPrelude) + "\n#line 1 \"user_kernels.cu\"\n" + body;
+
+    std::vector<std::string> opts = {arch, "-lineinfo", "--std=c++17", "-default-device"};
+    collect_options(user_src, &opts);
+    std::vector<const char*> copts;
+    for (auto& o : opts) copts.push_back(o.c_str());
+
+    nvrtcProgram prog = nullptr;
+    nvrtcResult r = nvrtcCreateProgram(&prog, full.c_str(), "ck_program.cu", 0, nullptr, nullptr);
+    if (r != NVRTC_SUCCESS) {
+        cb->err = 1000 + (int)r;
+        cb->log = std::string("nvrtcCreateProgram: ") + nvrtcGetErrorString(r);
+        return cb;
+    }
+    r = nvrtcCompileProgram(prog, (int)copts.size(), copts.data());
+    size_t logsz = 0;
+    nvrtcGetProgramLogSize(prog, &logsz);
+    if (logsz > 1) {
+        cb->log.resize(logsz);
+        nvrtcGetProgramLog(prog, &cb->log[0]);
+        while (!cb->log.empty() && cb->log.back() == '\0') cb->log.pop_back();
+    }
+    if (r != NVRTC_SUCCESS) {
+        cb->err = 1000 + (int)r;
+        cb->log = std::string("NVRTC build failed (") + nvrtcGetErrorString(r) + ") for " + arch + "\n" + cb->log;
+        nvrtcDestroyProgram(&prog);
+        return cb;  // failures are not cached: the caller may fix the source
+    }
+    size_t sz = 0;
+    r = nvrtcGetCUBINSize(prog, &sz);
+    if (r == NVRTC_SUCCESS && sz > 0) {
+        cb->image.resize(sz);
+        r = nvrtcGetCUBIN(prog, cb->image.data());
+    }
+    if (r != NVRTC_SUCCESS || sz == 0) {
+        cb->err = 1000 + (int)r;
+        cb->log += "\nnvrtcGetCUBIN failed";
+    }
+    nvrtcDestroyProgram(&prog);
+    if (cb->err == 0) {
+        std::lock_guard<std::mutex> lk(g_cache_mu);
+        g_cache[key] = cb;
+    }
+    return cb;
+}
+
+}  // namespace ck
+
+// Test hooks (exported, no GPU needed): lets the CPU test-suite check the source rewrite and that NVRTC can
+// build the shipped kernels for sm_100a without a device present.
+extern "C" {
+// returns a malloc'd, NUL-terminated rewritten source; caller frees with free()
+char* ckRewriteKernelSource(const char* src) {
+    std::string out = ck::rewrite_kernels(src ? src : "", nullptr);
+    char* p = (char*)malloc(out.size() + 1);
+    memcpy(p, out.c_str(), out.size() + 1);
+    return p;
+}
+// compiles `src` for sm_<major><minor>; returns 0 on success; *log_out (malloc'd) holds the build log
+int ckCompileCheck(const char* src, int cc_major, int cc_minor, char** log_out, long long* cubin_bytes) {
+    auto cb = ck::compile_source(src ? src : "", cc_major, cc_minor);
+    if (log_out) {
+        *log_out = (char*)malloc(cb->log.size() + 1);
+        memcpy(*log_out, cb->log.c_str(), cb->log.size() + 1);
+    }
+    if (cubin_bytes) *cubin_bytes = (long long)cb->image.size();
+    return cb->err;
+}
+// copies the cached cubin image for inspection with cuobjdump; returns bytes written (0 if absent/too small)
+long long ckCompileGetCubin(const char* src, int cc_major, int cc_minor, void* dst, long long cap) {
+    auto cb = ck::compile_source(src ? src : "", cc_major, cc_minor);
+    if (cb->err || (long long)cb->image.size() > cap) return 0;
+    memcpy(dst, cb->image.data(), cb->image.size());
+    return (long long)cb->image.size();
+}
+}

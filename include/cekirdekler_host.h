@@ -1,0 +1,99 @@
+/*
+ * cekirdekler_host.h — flat C view of libcekirdekler_host.so, the C++ host layer that stands where the
+ * reference's C# classes stand (there is no CLR on the build or GPU machines: SURVEY.md F6/F7).
+ *
+ * Each group mirrors one reference class; the file:line is the C# member it stands for (paths relative to
+ * /root/reference/Cekirdekler/Cekirdekler/).  Language bindings (the Python package cekirdekler_b200, via ctypes) wrap these
+ * into classes with the reference's names.  The library reaches the GPU only through include/KutuphaneCL.h.
+ *
+ * All functions are thread-compatible per object (the same rules as the C# classes they mirror); none throws.
+ */
+#ifndef CEKIRDEKLER_HOST_H
+#define CEKIRDEKLER_HOST_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef void* ckh_cruncher;  /* ClNumberCruncher */
+typedef void* ckh_array;     /* ClArray<T> */
+
+/* ---- Hardware.ClPlatforms.all().gpus() ------------------------------ ClObjectApi.cs:204, :390-404 */
+int32_t     ckh_gpu_count(void);
+const char* ckh_gpu_name(int32_t ordinal);              /* borrowed, valid until the next call on this thread */
+int32_t     ckh_gpu_compute_units(int32_t ordinal);
+uint64_t    ckh_gpu_memory_size(int32_t ordinal);
+
+/* ---- ClArray<T> / FastArr<T> ---------------------------------------- ClArray.cs:717-1907, CSpaceArrays.cs:234-577 */
+/* arrType: CSpaceArrays.ARR_* (FLOAT 0, DOUBLE 1, LONG 2, INT 3, UINT 4, BYTE 5, CHAR 6) */
+ckh_array ckh_array_create(int32_t arrType, int64_t n, int32_t alignmentBytes);   /* fastArr = true  */
+ckh_array ckh_array_wrap(void* userMemory, int32_t arrType, int64_t n);           /* a C# T[] */
+void      ckh_array_destroy(ckh_array a);
+void*     ckh_array_data(ckh_array a);
+int64_t   ckh_array_length(ckh_array a);
+int32_t   ckh_array_is_fast(ckh_array a);
+/* flag ids: 0 read, 1 partialRead, 2 write, 3 writeAll, 4 readOnly, 5 writeOnly, 6 zeroCopy (bools),
+ *           7 numberOfElementsPerWorkItem, 8 alignmentBytes (ints)                ClArray.cs:1742-1888 */
+void      ckh_array_set(ckh_array a, int32_t flagId, int32_t value);
+int32_t   ckh_array_get(ckh_array a, int32_t flagId);
+const char* ckh_array_flag_string(ckh_array a);          /* ClArray.cs:1685-1703; borrowed (thread-local) */
+
+/* ---- ClNumberCruncher ------------------------------------------------ ClNumberCruncher.cs:313-349 */
+ckh_cruncher ckh_cruncher_create(const int32_t* deviceOrdinals, int32_t nDevices, const char* kernelString,
+                                 int32_t noPipelining, int32_t computeQueueConcurrency, int32_t streamingEnabled);
+void        ckh_cruncher_destroy(ckh_cruncher c);
+int32_t     ckh_cruncher_error_code(ckh_cruncher c);                 /* :380-385 */
+const char* ckh_cruncher_error_message(ckh_cruncher c);              /* :387-392 */
+int32_t     ckh_cruncher_errors_happened(ckh_cruncher c);
+int32_t     ckh_cruncher_num_devices(ckh_cruncher c);
+const char* ckh_cruncher_device_name(ckh_cruncher c, int32_t i);     /* :296-299 */
+int32_t     ckh_cruncher_num_kernels(const char* kernelString);      /* kernel-name regex, :219-228 */
+const char* ckh_cruncher_kernel_name(const char* kernelString, int32_t i);
+/* property ids: 0 enqueueMode, 1 enqueueModeAsyncEnable, 2 noComputeMode, 3 fineGrainedQueueControl, 4 repeatCount,
+ *   5 performanceFeed, 6 smoothLoadBalancer, 7 balancerMode (0 reference, 1 adaptive), 8 deviceClock,
+ *   9 broadcastWholeReads                                            ClNumberCruncher.cs:66-187 */
+void        ckh_cruncher_set(ckh_cruncher c, int32_t propId, int32_t value);
+int32_t     ckh_cruncher_get(ckh_cruncher c, int32_t propId);
+void        ckh_cruncher_set_repeat_kernel_name(ckh_cruncher c, const char* name);
+int32_t     ckh_cruncher_markers_remaining(ckh_cruncher c);          /* :356-361 */
+int32_t     ckh_cruncher_markers_reached(ckh_cruncher c);            /* :367-372 */
+void        ckh_cruncher_flush_last_used_queue(ckh_cruncher c);      /* :141-145 */
+void        ckh_cruncher_sync(ckh_cruncher c);
+const char* ckh_cruncher_performance_report(ckh_cruncher c, int32_t computeId);   /* Cores.cs:994-1063 */
+/* fill `out` (capacity n) and return the number of devices the range is split over                  */
+int32_t     ckh_cruncher_ranges(ckh_cruncher c, int32_t computeId, int32_t* out, int32_t n);            /* Cores.globalRanges */
+int32_t     ckh_cruncher_references(ckh_cruncher c, int32_t computeId, int32_t* out, int32_t n);        /* Cores.globalReferences */
+int32_t     ckh_cruncher_benchmarks(ckh_cruncher c, int32_t computeId, double* out, int32_t n);         /* Cores.benchmarks, ms */
+int32_t     ckh_cruncher_normalized_compute_powers(ckh_cruncher c, double* out, int32_t n);             /* :254-270 */
+int32_t     ckh_cruncher_normalized_global_ranges(ckh_cruncher c, int32_t computeId, double* out, int32_t n); /* :277-294 */
+void        ckh_cruncher_reset_balancer(ckh_cruncher c, int32_t computeId);
+/* SPMD (one process per GPU): this cruncher's single device is global device `rank` of `world`;
+ * `exchange(times, world, user)` must all-gather the per-rank device times in place. */
+typedef void (*ckh_exchange_fn)(double* times, int32_t world, void* user);
+void        ckh_cruncher_set_spmd(ckh_cruncher c, int32_t rank, int32_t world, ckh_exchange_fn exchange, void* user);
+
+/* ---- ClParameterGroup.compute / ClArray.compute ---------------------- ClArray.cs:543-659, :1605-1736 */
+/* readWritesReady / elementsPerItemReady may be NULL (then each array's own flags are used).  Returns 0 when the
+ * compute was dispatched, otherwise the number of the validation rule that refused it. */
+int32_t ckh_compute(ckh_cruncher c, ckh_array* arrays, int32_t nArrays, int32_t computeId, const char* kernelNamesString,
+                    int32_t globalRange, int32_t localRange, int32_t ofsetGlobalRange, int32_t pipeline, int32_t pipelineType,
+                    int32_t pipelineBlobs, const char** readWritesReady, const int32_t* elementsPerItemReady);
+
+/* ---- Functions.loadBalance (pure host arithmetic) -------------------- HelperFunctions.cs:190-280, Cores.cs:569-605 */
+typedef void* ckh_balancer;
+ckh_balancer ckh_balancer_create(int32_t devices, int32_t mode /* 0 reference, 1 adaptive */);
+void         ckh_balancer_destroy(ckh_balancer b);
+/* One Cores.compute-style step: on the first call (all ranges 0) does the equal split + bench=10 pass; later calls use
+ * `benchmarkMs`.  `ranges` (in/out, `devices` ints) sums to totalRange afterwards. */
+void         ckh_balancer_step(ckh_balancer b, const double* benchmarkMs, int32_t smooth, int32_t totalRange, int32_t* ranges,
+                               int32_t pipelineEnabled, int32_t blobs, int32_t localRange);
+/* the raw reference function on caller-held state: history is kHistoryDepth(10) x devices doubles, oldest row first */
+void         ckh_load_balance(const double* benchmarkMs, int32_t smooth, double* history, int32_t totalRange, int32_t* ranges,
+                              int32_t step, int32_t devices);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* CEKIRDEKLER_HOST_H */

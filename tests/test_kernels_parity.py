@@ -1,0 +1,312 @@
+"""CUDA kernels, launched through ClNumberCruncher → libcekirdekler_host.so → the KutuphaneCL C ABI, against the CPU
+oracle on the same seeded inputs and against the committed golden fixtures.
+Bars: bit-exact for Mandelbrot iteration counts, vector-add, SAXPY (contraction off), 2-D n-body forces, blur, Sobel and
+the histogram; <= 1e-4 relative on 3-D n-body positions (the GPU uses the SFU reciprocal square root)."""
+import hashlib
+import json
+from pathlib import Path
+
+import numpy as np
+import pytest
+
+import cekirdekler_b200 as ck
+from cekirdekler_b200 import kernels
+from oracle import pyoracle as po
+
+pytestmark = pytest.mark.gpu
+GOLDEN = json.loads((Path(__file__).resolve().parent / "golden" / "kernel_vectors.json").read_text())
+
+
+def sha(a):
+    return hashlib.sha256(np.ascontiguousarray(a).tobytes()).hexdigest()
+
+
+def gpu0():
+    return ck.ClPlatforms.all().gpus()[0]
+
+
+def all_gpus():
+    return ck.ClPlatforms.all().gpus()
+
+
+# ------------------------------------------------------------------ Mandelbrot (K1)
+def run_mandelbrot(devs, W, H, max_iter, kernel="mandelbrot", calls=1, pipeline=False, pipeline_type=True, blobs=4):
+    cr = ck.ClNumberCruncher(devs, kernels.source("mandelbrot"))
+    assert cr.errorCode() == 0, cr.errorMessage()
+    view = ck.ClArray(8, np.float32)
+    view.view[:] = po.mandelbrot_view(W, H, max_iter)
+    view.readOnly = True                      # whole-array `read` input (scalars travel in arrays: F9)
+    out = ck.ClArray(W * H, np.int32)
+    out.writeOnly = True                      # sliced `write` output
+    e = 4 if kernel == "mandelbrot" else 1
+    out.numberOfElementsPerWorkItem = e
+    for _ in range(calls):
+        out.view[:] = -1
+        rc = view.nextParam(out).compute(cr, 1, kernel, W * H // e, 256, 0, pipeline, pipeline_type, blobs)
+        assert rc == 0
+    return out.view.copy(), cr
+
+
+def test_mandelbrot_c1_bit_exact_against_oracle_and_golden(gpus):
+    got, _ = run_mandelbrot(gpu0(), 1024, 1024, 256)
+    exp = po.mandelbrot(po.mandelbrot_view(1024, 1024, 256), 1024 * 1024)
+    assert np.array_equal(got, exp)
+    g = GOLDEN["mandelbrot_c1"]
+    assert sha(got) == g["sha256"] and int(got.sum()) == g["sum"]
+    crop = np.array(g["crop_rows_480_544_cols_200_264"], np.int32)
+    assert np.array_equal(got.reshape(1024, 1024)[480:544, 200:264], crop)
+
+
+@pytest.mark.parametrize("kernel", ["mandelbrot", "mandelbrot1"])
+@pytest.mark.parametrize("max_iter", [1, 15, 16, 17, 100, 1000])
+def test_mandelbrot_iteration_limits(gpus, kernel, max_iter):
+    # max_iter around the unchecked-block length (16) exercises the block/tail/replay boundaries
+    got, _ = run_mandelbrot(gpu0(), 512, 256, max_iter, kernel)
+    exp = po.mandelbrot(po.mandelbrot_view(512, 256, max_iter), 512 * 256)
+    assert np.array_equal(got, exp)
+
+
+def test_mandelbrot_zoomed_views_bit_exact(gpus):
+    cr = ck.ClNumberCruncher(gpu0(), kernels.source("mandelbrot"))
+    W = H = 512
+    out = ck.ClArray(W * H, np.int32)
+    out.writeOnly = True
+    out.numberOfElementsPerWorkItem = 4
+    view = ck.ClArray(8, np.float32)
+    view.readOnly = True
+    for (x0, x1, y0, y1, it) in [(-2.0, -1.9, -0.05, 0.05, 2000), (-0.75, -0.74, 0.1, 0.11, 3000),
+                                 (-2.5, 2.5, -2.5, 2.5, 64), (0.25, 0.26, 0.0, 0.01, 4096)]:
+        v = po.mandelbrot_view(W, H, it, x0, x1, y0, y1)
+        view.view[:] = v
+        assert view.nextParam(out).compute(cr, 7, "mandelbrot", W * H // 4, 256) == 0
+        assert np.array_equal(out.view, po.mandelbrot(v, W * H)), (x0, x1, y0, y1)
+
+
+def test_mandelbrot_c3_strided_sample_matches_golden(gpus):
+    """Full C3 size (16384^2 x 4096) on the GPU; checked on the committed strided oracle sample and by the
+    size-independent property that the image is symmetric about the real axis (rows y and H-1-y... the view is
+    symmetric: cy(py) = -cy(H-py) exactly only for py and H-py, so rows 1..H-1 mirror)."""
+    g = GOLDEN["mandelbrot_c3_sample"]
+    W = H = 16384
+    got, _ = run_mandelbrot(gpu0(), W, H, 4096)
+    idx = g["offset"] + g["stride"] * np.arange(g["count"], dtype=np.int64)
+    sample = got[idx]
+    assert sha(sample.astype(np.int32)) == g["sha256"] and int(sample.sum()) == g["sum"]
+    img = got.reshape(H, W)
+    # cy = fma(py, dy, y0) with y0 = -1.5, dy = 3/16384 (exact in binary): cy(py) == -cy(H - py) bit-for-bit, and the
+    # iteration is symmetric under conjugation, so row py equals row H - py for py in [1, H-1]
+    assert np.array_equal(img[1:H // 2], img[H - 1:H // 2:-1])
+
+
+def test_mandelbrot_multi_gpu_balanced_and_pipelined(gpus):
+    W, H, it = 2048, 2048, 512
+    exp = po.mandelbrot(po.mandelbrot_view(W, H, it), W * H)
+    got, cr = run_mandelbrot(all_gpus(), W, H, it, calls=6)
+    assert np.array_equal(got, exp)
+    r = cr.globalRanges(1)
+    assert sum(r) == W * H // 4 and all(x % 256 == 0 for x in r)
+    for ptype in (True, False):
+        got, _ = run_mandelbrot(all_gpus(), W, H, it, calls=3, pipeline=True, pipeline_type=ptype, blobs=8)
+        assert np.array_equal(got, exp)
+
+
+# ------------------------------------------------------------------ vector-add / SAXPY (K2, K3)
+def test_reference_vector_add_test(gpus):
+    """Tester.stream_C_equals_A_plus_B_1M_elements (Tester.cs:7806-7843): API style 2 flag strings, driver pipeline with
+    8 blobs, local 256, mixed array kinds (native array, language array, ClArray), 10 calls; the reference checks c[700]."""
+    n = 1024 * 1024
+    a = ck.ClFloatArray(n)
+    b_host = np.arange(n, dtype=np.float32)
+    b = ck.ClArray(b_host)
+    c = ck.ClArray(n, np.float32)
+    a.view[:] = 3
+    c.view[:] = 105
+    cr = ck.ClNumberCruncher(all_gpus(), kernels.REFERENCE_VECTOR_ADD)
+    assert cr.errorCode() == 0, cr.errorMessage()
+    g = a.nextParam(b, c)
+    for _ in range(10):
+        rc = g.compute(cr, 1, "vectorAdd", n, 256, 0, True, ck.PIPELINE_DRIVER, 8,
+                       readWritesReady=["partial read", "partial read", "write"], elementsPerItemReady=[1, 1, 1])
+        assert rc == 0
+    assert abs(c[700] - (a[700] + b[700])) < 0.5       # the reference's own check
+    exp = np.zeros(n, np.float32)
+    po.vector_add(a.view, b_host, exp)
+    assert np.array_equal(c.view, exp)                  # and bit-exact everywhere
+
+
+@pytest.mark.parametrize("mode", ["plain", "event", "driver"])
+def test_vector_add4_and_saxpy4_bit_exact(gpus, mode):
+    n = 1 << 22
+    cr = ck.ClNumberCruncher(all_gpus(), kernels.source("stream"))
+    assert cr.errorCode() == 0, cr.errorMessage()
+    a, b, c = ck.ClFloatArray(n), ck.ClFloatArray(n), ck.ClFloatArray(n)
+    a.view[:] = po.uniform(1, n, -100, 100)
+    b.view[:] = po.uniform(2, n, -100, 100)
+    for arr in (a, b):
+        arr.partialRead, arr.read, arr.readOnly = True, False, True
+        arr.numberOfElementsPerWorkItem = 4
+    c.writeOnly = True
+    c.numberOfElementsPerWorkItem = 4
+    pipe = mode != "plain"
+    for _ in range(3):
+        assert a.nextParam(b, c).compute(cr, 1, "vectorAdd4", n // 4, 256, 0, pipe, mode == "event", 16) == 0
+    exp = np.zeros(n, np.float32)
+    po.vector_add(a.view, b.view, exp)
+    assert np.array_equal(c.view, exp)
+
+    alpha = ck.ClFloatArray(1)
+    alpha[0] = 2.0
+    alpha.readOnly = True
+    x, y = a, ck.ClFloatArray(n)
+    y.view[:] = b.view
+    y.partialRead, y.read = True, False
+    y.numberOfElementsPerWorkItem = 4
+    exp = b.view.copy()
+    for _ in range(2):
+        assert alpha.nextParam(x, y).compute(cr, 2, "saxpy4", n // 4, 256, 0, pipe, mode == "event", 16) == 0
+        po.saxpy(alpha.view, x.view, exp)
+    assert np.array_equal(y.view, exp)
+
+
+def test_saxpy_scalar_kernel_and_exactly_representable_inputs(gpus):
+    # BASELINE's C2 inputs: a[i] = 3, b[i] = i mod 2^20, alpha = 2 → every sum is exact
+    n = 1 << 20
+    cr = ck.ClNumberCruncher(gpu0(), kernels.source("stream"))
+    alpha, x, y = ck.ClFloatArray(1), ck.ClFloatArray(n), ck.ClFloatArray(n)
+    alpha[0] = 2.0
+    x.view[:] = 3
+    y.view[:] = np.arange(n) % (1 << 20)
+    alpha.readOnly = True
+    x.readOnly = True
+    assert alpha.nextParam(x, y).compute(cr, 1, "saxpy", n, 256) == 0
+    assert np.array_equal(y.view, (6 + np.arange(n) % (1 << 20)).astype(np.float32))
+
+
+# ------------------------------------------------------------------ n-body (K4)
+def test_nbody2d_reference_kernel_text_and_tiled_kernel(gpus):
+    """Tester.nBody (Tester.cs:7682-7799) at n = 8192, local 64: the reference's own kernel text (n spliced in) and the
+    shared-memory-tiled restatement, both against the reference's host loop (oracle_nbody2d).  The reference accepts
+    ±0.01 absolute; here both are bit-exact."""
+    n = 8192
+    x, y = po.uniform(0xC0FFEE, n, -15, 15), po.uniform(0xC0FFEE + 1, n, -15, 15)
+    fx_exp, fy_exp = np.zeros(n, np.float32), np.zeros(n, np.float32)
+    po.nbody2d(x, y, fx_exp, fy_exp)
+
+    cr = ck.ClNumberCruncher(all_gpus(), kernels.reference_nbody_kernel(n))
+    assert cr.errorCode() == 0, cr.errorMessage()
+    fx, fy = np.zeros(n, np.float32), np.zeros(n, np.float32)
+    xc, yc, fxc, fyc = ck.ClArray(x), ck.ClArray(y), ck.ClArray(fx), ck.ClArray(fy)
+    for _ in range(5):
+        assert xc.nextParam(yc, fxc, fyc).compute(cr, 1, "nBody", n, 64) == 0
+    assert np.all(np.abs(fx - fx_exp) <= 0.01) and np.all(np.abs(fy - fy_exp) <= 0.01)   # the reference's check
+    assert np.array_equal(fx, fx_exp) and np.array_equal(fy, fy_exp)
+
+    cr2 = ck.ClNumberCruncher(all_gpus(), kernels.source("nbody"))
+    assert cr2.errorCode() == 0, cr2.errorMessage()
+    fx2, fy2 = ck.ClFloatArray(n), ck.ClFloatArray(n)
+    nn = ck.ClIntArray(1)
+    nn[0] = n
+    nn.readOnly = True
+    xc.readOnly, yc.readOnly = True, True
+    fx2.writeOnly, fy2.writeOnly = True, True
+    assert xc.nextParam(yc, fx2, fy2, nn).compute(cr2, 1, "nBody2D", n, 256) == 0
+    assert np.array_equal(fx2.view, fx_exp) and np.array_equal(fy2.view, fy_exp)
+
+
+def test_nbody2d_golden(gpus):
+    n = 1024
+    g = GOLDEN["nbody2d_1024"]
+    x, y = po.uniform(g["seed_x"], n, -15, 15), po.uniform(g["seed_y"], n, -15, 15)
+    cr = ck.ClNumberCruncher(gpu0(), kernels.source("nbody"))
+    fx, fy, nn = ck.ClFloatArray(n), ck.ClFloatArray(n), ck.ClIntArray(1)
+    nn[0] = n
+    xc, yc = ck.ClArray(x), ck.ClArray(y)
+    assert xc.nextParam(yc, fx, fy, nn).compute(cr, 1, "nBody2D", n, 256) == 0
+    assert sha(fx.view) == g["sha256_fx"]
+    assert np.array_equal(fx.view[:8], np.array(g["fx_head"], np.float32))
+
+
+def nbody3d_inputs(n, seed=0xC0FFEE + 10):
+    pos = np.zeros((n, 4), np.float32)
+    for c in range(3):
+        pos[:, c] = po.uniform(seed + c, n, -15, 15)
+    pos[:, 3] = 1.0
+    return pos
+
+
+@pytest.mark.parametrize("n,steps", [(2048, 1), (16384, 10)])
+def test_nbody3d_positions_within_1e4_relative(gpus, n, steps):
+    pos0 = nbody3d_inputs(n)
+    params_h = np.array([1e-3, 1e-4, n, 0], np.float32)
+    # oracle
+    p, v, o = pos0.copy().reshape(-1), np.zeros(4 * n, np.float32), np.zeros(4 * n, np.float32)
+    for _ in range(steps):
+        po.nbody3d_step(p, v, o, params_h)
+        p, o = o, p
+    # GPU: pos is a whole-array read (broadcast to every device), vel/posOut are sliced 4 floats per work-item
+    cr = ck.ClNumberCruncher(all_gpus(), kernels.source("nbody"))
+    assert cr.errorCode() == 0, cr.errorMessage()
+    pa, pb, vel, params = ck.ClFloatArray(4 * n), ck.ClFloatArray(4 * n), ck.ClFloatArray(4 * n), ck.ClFloatArray(4)
+    pa.view[:] = pos0.reshape(-1)
+    params.view[:] = params_h
+    params.readOnly = True
+    vel.partialRead, vel.read = True, False
+    vel.numberOfElementsPerWorkItem = 4
+    for arr in (pa, pb):
+        arr.numberOfElementsPerWorkItem = 4
+    src, dst = pa, pb
+    for _ in range(steps):
+        src.read, src.partialRead, src.write = True, False, False      # input: whole array to every device
+        dst.read, dst.partialRead, dst.write = False, False, True      # output: each device's slice
+        assert src.nextParam(vel, dst, params).compute(cr, 1, "nBody3D", n, 256) == 0
+        src, dst = dst, src
+    got = src.view.reshape(n, 4)
+    exp = p.reshape(n, 4)
+    rel = np.abs(got[:, :3] - exp[:, :3]) / np.maximum(np.abs(exp[:, :3]), 1e-3)
+    assert rel.max() <= 1e-4, rel.max()
+    assert np.array_equal(got[:, 3], exp[:, 3])
+    if n == 2048:
+        g = GOLDEN["nbody3d_2048"]
+        ref = np.array(g["pos_out_head"], np.float32)
+        assert np.allclose(got[:4], ref, rtol=1e-4, atol=1e-6)
+
+
+# ------------------------------------------------------------------ blur → Sobel → histogram (K5)
+@pytest.mark.parametrize("W,H", [(256, 128), (3840, 2160)])
+def test_image_chain_bit_exact(gpus, W, H):
+    n = W * H
+    img = po.uniform(0xF00D, n, 0, 1)
+    dims_h = np.array([W, H], np.int32)
+    b_exp, s_exp, h_exp = np.zeros(n, np.float32), np.zeros(n, np.float32), np.zeros(256, np.uint32)
+    po.blur5x5(img, b_exp, dims_h)
+    po.sobel(b_exp, s_exp, dims_h)
+    po.histogram(s_exp, h_exp)
+    if (W, H) == (256, 128):
+        g = GOLDEN["image_256x128"]
+        assert sha(b_exp) == g["sha256_blur"] and sha(s_exp) == g["sha256_sobel"] and h_exp.tolist() == g["hist"]
+
+    cr = ck.ClNumberCruncher(gpu0(), kernels.source("image"))
+    assert cr.errorCode() == 0, cr.errorMessage()
+    src, blur, sob, hist, dims = ck.ClFloatArray(n), ck.ClFloatArray(n), ck.ClFloatArray(n), ck.ClUIntArray(256), ck.ClIntArray(2)
+    src.view[:] = img
+    dims.view[:] = dims_h
+    dims.readOnly = True
+    src.readOnly = True                    # whole-array read: a stencil needs its neighbours' rows
+    blur.writeOnly = True
+    assert src.nextParam(blur, dims).compute(cr, 1, "gaussianBlur", n, 256) == 0
+    assert np.array_equal(blur.view, b_exp)
+    blur.writeOnly = False
+    blur.readOnly = True
+    sob.writeOnly = True
+    assert blur.nextParam(sob, dims).compute(cr, 2, "sobel", n, 256) == 0
+    assert np.array_equal(sob.view, s_exp)
+    sob.writeOnly = False
+    sob.readOnly = True
+    sob.numberOfElementsPerWorkItem = 16
+    hist.writeOnly = True
+    hist.writeAll = True                   # the whole 256-bin array comes back from one device
+    hist.view[:] = 12345
+    for _ in range(2):                     # twice: the zeroing kernel makes the counts replace, not accumulate
+        assert sob.nextParam(hist).compute(cr, 3, "histogramZero histogram", n // 16, 256) == 0
+    assert np.array_equal(hist.view, h_exp)
+    assert int(hist.view.sum()) == n       # a checksum that holds at any size

@@ -1,0 +1,80 @@
+"""Kernel-source front-end on a CPU-only box: the signature rewrite, and that NVRTC builds every shipped kernel source
+(and the reference's own kernel strings) for sm_100a without a device."""
+import ctypes as C
+
+import pytest
+
+from cekirdekler_b200 import kernels
+from cekirdekler_b200._native import shim
+
+
+def rewrite(src: str) -> str:
+    L = shim()
+    L.ckRewriteKernelSource.restype = C.c_void_p
+    L.ckRewriteKernelSource.argtypes = [C.c_char_p]
+    p = L.ckRewriteKernelSource(src.encode())
+    try:
+        return C.string_at(p).decode()
+    finally:
+        C.CDLL(None).free(C.c_void_p(p))
+
+
+def compile_check(src: str):
+    L = shim()
+    L.ckCompileCheck.argtypes = [C.c_char_p, C.c_int, C.c_int, C.POINTER(C.c_char_p), C.POINTER(C.c_longlong)]
+    log, nbytes = C.c_char_p(), C.c_longlong()
+    rc = L.ckCompileCheck(src.encode(), 10, 0, C.byref(log), C.byref(nbytes))
+    return rc, (log.value or b"").decode(errors="replace"), nbytes.value
+
+
+def test_rewrite_adds_the_hidden_offset_parameter():
+    out = rewrite("__kernel void f(__global float* a, __global int* b) { a[get_global_id(0)] = b[0]; }")
+    assert 'extern "C" __global__ void f(const unsigned int __ck_goff, __global float* a, __global int* b)' in out
+    out = rewrite("kernel void g(void) { }\nkernel void h() { }")
+    assert "void g(const unsigned int __ck_goff)" in out and "void h(const unsigned int __ck_goff)" in out
+
+
+def test_rewrite_leaves_comments_strings_and_lookalikes_alone():
+    src = '// __kernel void c(int x)\n/* kernel void d(int x) */\nconst char* s = "kernel void e(";\nint my_kernel = 3; void kernelize(int q);'
+    assert rewrite(src) == src
+
+
+@pytest.mark.parametrize("name", ["stream", "mandelbrot", "nbody", "image"])
+def test_shipped_kernels_build_for_sm_100a(name):
+    rc, log, nbytes = compile_check(kernels.source(name))
+    assert rc == 0, log
+    assert nbytes > 1000
+
+
+@pytest.mark.parametrize("src", [
+    kernels.reference_copy_kernel("uchar"), kernels.reference_copy_kernel("double"), kernels.reference_copy_kernel("long"),
+    kernels.REFERENCE_COPY_KERNEL_CHAR, kernels.REFERENCE_VECTOR_ADD, kernels.reference_nbody_kernel(8192),
+])
+def test_reference_opencl_strings_build_unmodified(src):
+    rc, log, _ = compile_check(src)
+    assert rc == 0, log
+
+
+def test_opencl_c_idioms_compile_through_the_prelude():
+    src = """
+    float helper(float x) { return mad(x, 2.0f, 1.0f); }
+    __kernel void k(__global float* a, __global const float* b, __global int* hist)
+    {
+        __local float tile[64];
+        int l = get_local_id(0);
+        int i = get_global_id(0);
+        tile[l] = b[i];
+        barrier(CLK_LOCAL_MEM_FENCE);
+        float4 v = make_float4(tile[l], 1.0f, 2.0f, 3.0f);
+        v = v * 2.0f + v;
+        a[i] = helper(native_sqrt(dot(v, v))) + (float)get_group_id(0) + (float)get_local_size(0);
+        atomic_add(&hist[i % 16], 1);
+        atomic_inc(&hist[0]);
+    }"""
+    rc, log, _ = compile_check(src)
+    assert rc == 0, log
+
+
+def test_build_errors_are_reported_not_thrown():
+    rc, log, nbytes = compile_check("__kernel void broken(__global float* a) { a[0] = undefined_symbol; }")
+    assert rc != 0 and "undefined_symbol" in log and nbytes == 0
