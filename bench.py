@@ -394,7 +394,7 @@ def run_ours(args):
         sel = mine[idx]
         parity = {"sample_pixels_checked": int(sel.sum()), "mismatches": int((out.view[idx[sel]] != s["values"][sel]).sum())}
         line_cpu = {"value": s["pixels"] / s["seconds"] / 1e6, "unit": UNIT, "cores": po.threads(), "kind": "port",
-                    "sample": f"{s['pixels']} pixels (every {s['stride']}th of the {W}x{H} image), {s['iters']} iterations, {s['seconds']:.1f} s"}
+                    "sample": f"{s['pixels']} pixels (odd stride {s['stride']} across the whole {W}x{H} image), {s['iters']} iterations, {s['seconds']:.1f} s"}
 
     flops = 8.0 * total_iters
     peak_tf = 2.0 * 128 * sms * pk["sm_max_mhz"] * 1e6 / 1e12

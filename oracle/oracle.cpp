@@ -79,19 +79,18 @@ void oracle_nbody2d(const float* x, const float* y, float* fx, float* fy, int n,
 // view = { x0, y0, dx, dy, (float)W, (float)maxIter, 0, 0 }.  Pixel p: px = p % W, py = p / W,
 //   cx = fmaf(px, dx, x0), cy = fmaf(py, dy, y0), z0 = 0.
 // out[p] = the first k in [0, maxIter) with fmaf(x_k, x_k, y_k*y_k) > 4, else maxIter, where
-//   x_{k+1} = fmaf(x_k, x_k, cx - y_k*y_k),   y_{k+1} = fmaf(x_k + x_k, y_k, cy).
-// 5 rounded operations per iteration; by convention the work is counted as 8 FLOP per executed iteration
+//   x_{k+1} = fmaf(x_k, x_k, fmaf(-y_k, y_k, cx)),   y_{k+1} = fmaf(2, x_k*y_k, cy).
+// 4 rounded operations per iteration (+2 for the escape test); by convention the work is counted as 8 FLOP per executed iteration
 // (3 mul + 5 add of the textbook form).
 static inline int mandel_pixel(float cx, float cy, int maxIter) {
     float x = 0.0f, y = 0.0f;
     int k = 0;
     while (k < maxIter) {
-        float yy = y * y;
-        float m = fmaf(x, x, yy);
+        float m = fmaf(x, x, y * y);
         if (m > 4.0f) break;
-        float t = cx - yy;
-        float x2 = x + x;
-        y = fmaf(x2, y, cy);
+        float t = fmaf(-y, y, cx);
+        float w = x * y;
+        y = fmaf(2.0f, w, cy);
         x = fmaf(x, x, t);
         k++;
     }
