@@ -122,6 +122,7 @@ def cpu_sample(po, view, seconds_target=12.0):
     pix_per_s = probe / max(time.perf_counter() - t0, 1e-3)
     count = int(max(probe, min(npix // 3, pix_per_s * seconds_target)))
     stride = max(3, (npix - 1000) // count) | 1
+    count = min(count, (npix - 1000) // stride)   # the last sample index stays inside the image
     buf = np.zeros(count, np.int32)
     t0 = time.perf_counter()
     iters = po.mandelbrot_sample(view, 777, stride, count, buf)

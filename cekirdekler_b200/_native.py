@@ -144,6 +144,17 @@ def host() -> C.CDLL:
             "ckh_balancer_create": (vp, [i32, i32]), "ckh_balancer_destroy": (None, [vp]),
             "ckh_balancer_step": (None, [vp, pdbl, i32, i32, pi32, i32, i32, i32]),
             "ckh_load_balance": (None, [pdbl, i32, pdbl, i32, pi32, i32, i32]),
+            "ckh_stage_create": (vp, [i32]), "ckh_stage_destroy": (None, [vp]),
+            "ckh_stage_add_devices": (None, [vp, pi32, i32]),
+            "ckh_stage_add_kernels": (None, [vp, cp, cp, pi32, pi32, i32]),
+            "ckh_stage_initializer_kernel": (None, [vp, cp, pi32, pi32, i32]),
+            "ckh_stage_add_buffer": (None, [vp, i32, i32, i64, i32]),
+            "ckh_stage_prepend_to": (None, [vp, vp]), "ckh_stage_append_to": (None, [vp, vp]),
+            "ckh_stage_set_enqueue_mode": (None, [vp, i32]), "ckh_stage_make_pipeline": (vp, [vp, i32]),
+            "ckh_pipeline_destroy": (None, [vp]),
+            "ckh_pipeline_push": (i32, [vp, C.POINTER(vp), i32, C.POINTER(vp), i32]),
+            "ckh_pipeline_error_code": (i32, [vp]), "ckh_pipeline_error_message": (cp, [vp]),
+            "ckh_pipeline_forwarding": (i32, [vp]), "ckh_pipeline_counter": (i32, [vp]),
         }
         for name, (res, args) in sig.items():
             fn = getattr(L, name)

@@ -271,3 +271,45 @@ void ckh_load_balance(const double* benchMs, int32_t smooth, double* history, in
 }
 
 }  // extern "C"
+
+// ------------------------------------------------------------------ device-to-device pipeline (ClPipeline.cs:41-2356)
+#include "pipeline.h"
+
+extern "C" {
+
+ckh_stage ckh_stage_create(int32_t debugLog) { return new ClPipelineStage(debugLog != 0); }
+void ckh_stage_destroy(ckh_stage s) { delete static_cast<ClPipelineStage*>(s); }
+#define ST(s) (*static_cast<ClPipelineStage*>(s))
+void ckh_stage_add_devices(ckh_stage s, const int32_t* ords, int32_t n) {
+    if (s) ST(s).addDevices(std::vector<int>(ords, ords + (n > 0 ? n : 0)));
+}
+void ckh_stage_add_kernels(ckh_stage s, const char* kernels, const char* names, const int32_t* globals, const int32_t* locals, int32_t n) {
+    if (s) ST(s).addKernels(kernels ? kernels : "", names ? names : "", std::vector<int>(globals, globals + n), std::vector<int>(locals, locals + n));
+}
+void ckh_stage_initializer_kernel(ckh_stage s, const char* names, const int32_t* globals, const int32_t* locals, int32_t n) {
+    if (s) ST(s).initializerKernel(names ? names : "", std::vector<int>(globals, globals + n), std::vector<int>(locals, locals + n));
+}
+void ckh_stage_add_buffer(ckh_stage s, int32_t role, int32_t arrType, int64_t n, int32_t elementsPerWorkItem) {
+    if (!s) return;
+    if (role == 0) ST(s).addInputBuffer(arrType, n, elementsPerWorkItem);
+    else if (role == 1) ST(s).addOutputBuffer(arrType, n, elementsPerWorkItem);
+    else ST(s).addHiddenBuffer(arrType, n, elementsPerWorkItem);
+}
+void ckh_stage_prepend_to(ckh_stage s, ckh_stage other) { if (s) ST(s).prependToStage(static_cast<ClPipelineStage*>(other)); }
+void ckh_stage_append_to(ckh_stage s, ckh_stage other) { if (s) ST(s).appendToStage(static_cast<ClPipelineStage*>(other)); }
+void ckh_stage_set_enqueue_mode(ckh_stage s, int32_t v) { if (s) ST(s).enqueueMode = (v != 0); }
+ckh_pipeline ckh_stage_make_pipeline(ckh_stage s, int32_t hostForwarding) {
+    return s ? ST(s).makePipeline(hostForwarding ? Forwarding::Host : Forwarding::PeerToPeer) : nullptr;
+}
+void ckh_pipeline_destroy(ckh_pipeline p) { delete static_cast<ClPipeline*>(p); }
+int32_t ckh_pipeline_push(ckh_pipeline p, void** data, int32_t nData, void** results, int32_t nResults) {
+    if (!p) return 0;
+    std::vector<void*> d(data, data + (data ? nData : 0)), r(results, results + (results ? nResults : 0));
+    return static_cast<ClPipeline*>(p)->pushData(d, r) ? 1 : 0;
+}
+int32_t ckh_pipeline_error_code(ckh_pipeline p) { return p ? static_cast<ClPipeline*>(p)->errorCode() : 1; }
+const char* ckh_pipeline_error_message(ckh_pipeline p) { return keep(p ? static_cast<ClPipeline*>(p)->errorMessage() : "null pipeline"); }
+int32_t ckh_pipeline_forwarding(ckh_pipeline p) { return p ? (int32_t)static_cast<ClPipeline*>(p)->forwarding() : -1; }
+int32_t ckh_pipeline_counter(ckh_pipeline p) { return p ? static_cast<ClPipeline*>(p)->counter : 0; }
+
+}  // extern "C"

@@ -1,0 +1,264 @@
+// pipeline.cpp — see pipeline.h.  Reference: ClPipeline.cs:41-139 (pushData), :146-603 (stage run), :624-1575
+// (forwardResults), :1582-1873 (stage building), :1886-2356 (stage buffers).
+#include "pipeline.h"
+
+#include <cstdio>
+#include <cstring>
+
+namespace cekirdekler {
+
+// ------------------------------------------------------------------ stage buffers
+ClPipelineStageBuffer::ClPipelineStageBuffer(int arrType, int64_t n, int elementsPerWorkItem)
+    : a_(new ClArray(arrType, n)), b_(new ClArray(arrType, n)), cur_(a_.get()), dup_(b_.get()) {
+    a_->numberOfElementsPerWorkItem = elementsPerWorkItem;
+    b_->numberOfElementsPerWorkItem = elementsPerWorkItem;
+}
+
+// ------------------------------------------------------------------ stage building
+static std::vector<std::string> splitNames(const std::string& s) {
+    std::vector<std::string> out;
+    std::string cur;
+    for (char c : s) {
+        if (c == ' ' || c == ',' || c == ';' || c == '-' || c == '\n' || c == '@' || c == '\t' || c == '\r') {
+            if (!cur.empty()) out.push_back(cur);
+            cur.clear();
+        } else {
+            cur.push_back(c);
+        }
+    }
+    if (!cur.empty()) out.push_back(cur);
+    return out;
+}
+
+void ClPipelineStage::addKernels(const std::string& kernels, const std::string& kernelNames, const std::vector<int>& globalRanges,
+                                 const std::vector<int>& localRanges) {
+    kernelsToCompile_ += "\n" + kernels;
+    auto names = splitNames(kernelNames);
+    for (size_t i = 0; i < names.size(); i++) {
+        const int g = i < globalRanges.size() ? globalRanges[i] : (globalRanges.empty() ? 0 : globalRanges.back());
+        const int l = i < localRanges.size() ? localRanges[i] : (localRanges.empty() ? 256 : localRanges.back());
+        kernels_.push_back({names[i], g, l});
+    }
+}
+
+void ClPipelineStage::initializerKernel(const std::string& kernelNames, const std::vector<int>& globalRanges,
+                                        const std::vector<int>& localRanges) {
+    auto names = splitNames(kernelNames);
+    for (size_t i = 0; i < names.size(); i++) {
+        const int g = i < globalRanges.size() ? globalRanges[i] : (globalRanges.empty() ? 0 : globalRanges.back());
+        const int l = i < localRanges.size() ? localRanges[i] : (localRanges.empty() ? 256 : localRanges.back());
+        initKernels_.push_back({names[i], g, l});
+    }
+}
+
+ClPipelineStageBuffer* ClPipelineStage::addInputBuffer(int arrType, int64_t n, int e) {
+    inputs_.emplace_back(new ClPipelineStageBuffer(arrType, n, e));
+    return inputs_.back().get();
+}
+ClPipelineStageBuffer* ClPipelineStage::addOutputBuffer(int arrType, int64_t n, int e) {
+    outputs_.emplace_back(new ClPipelineStageBuffer(arrType, n, e));
+    return outputs_.back().get();
+}
+ClPipelineStageBuffer* ClPipelineStage::addHiddenBuffer(int arrType, int64_t n, int e) {
+    hiddens_.emplace_back(new ClPipelineStageBuffer(arrType, n, e));
+    return hiddens_.back().get();
+}
+
+void ClPipelineStage::prependToStage(ClPipelineStage* stage) {
+    next_ = stage;
+    if (stage) stage->previous_ = this;
+}
+void ClPipelineStage::appendToStage(ClPipelineStage* stage) {
+    previous_ = stage;
+    if (stage) stage->next_ = this;
+}
+
+ClPipelineStage::~ClPipelineStage() {
+    if (forwardQueue_) {
+        finish(forwardQueue_);
+        deleteCommandQueue(forwardQueue_);
+    }
+    if (forwardCtx_) deleteContext(forwardCtx_);
+    if (forwardDev_) deleteDevice(forwardDev_);
+    if (forwardPlat_) deletePlatform(forwardPlat_);
+}
+
+ClPipeline* ClPipelineStage::makePipeline(Forwarding mode) {
+    // walk back to the first stage, then forward: one stage per layer, linear chains only (ClPipeline.cs:1596-1600)
+    ClPipelineStage* first = this;
+    while (first->previous_) first = first->previous_;
+    auto* p = new ClPipeline();
+    for (ClPipelineStage* s = first; s; s = s->next_) {
+        p->stages_.push_back(s);
+        if (s->devices_.size() != 1) mode = Forwarding::Host;  // a multi-device stage splits its buffers: keep the host path
+    }
+    p->mode_ = mode;
+    for (auto* s : p->stages_) s->init(mode);
+    return p;
+}
+
+bool ClPipelineStage::init(Forwarding mode) {
+    if (initComplete_) return errorCode() == 0;
+    initComplete_ = true;
+    if (devices_.empty()) {
+        initError_ = 1;
+        initMessage_ = "pipeline stage has no devices";
+        return false;
+    }
+    // "can't enable driver-pipelining but can have more device-pipeline-stages": noPipelining = true (ClPipeline.cs:231)
+    cruncher_.reset(new ClNumberCruncher(devices_, kernelsToCompile_, true));
+    if (cruncher_->errorCode() != 0) return false;
+    // a queue of our own on the stage's (first) device for incoming hand-offs and end-of-pipeline transfers
+    ck_handle list = platformList();
+    forwardPlat_ = createPlatform(list, 0);
+    deletePlatformList(list);
+    forwardDev_ = createDevice(forwardPlat_, CODE_GPU(), devices_[0]);
+    forwardCtx_ = forwardDev_ ? createContext(forwardPlat_, forwardDev_) : nullptr;
+    forwardQueue_ = forwardCtx_ ? createCommandQueue(forwardCtx_, forwardDev_, 0) : nullptr;
+    if (!forwardQueue_) {
+        initError_ = 1;
+        initMessage_ = std::string("pipeline stage: cannot create the hand-off queue: ") + ckGetLastError();
+        return false;
+    }
+    if (!initKernels_.empty()) run(true, mode);
+    return true;
+}
+
+std::vector<ArrayRef> ClPipelineStage::parameterRefs(Forwarding mode) const {
+    // parameter order: inputs, hidden, outputs (ClPipeline.cs:281-370); flags as :236-270
+    std::vector<ArrayRef> refs;
+    for (auto& b : inputs_) {
+        ArrayRef r = b->buf()->ref();
+        r.flags = (mode == Forwarding::Host) ? F_READ : 0u;  // P2P: the data is already in HBM (arrived by hand-off)
+        refs.push_back(r);
+    }
+    for (auto& b : hiddens_) {
+        ArrayRef r = b->buf()->ref();
+        r.flags = 0u;
+        refs.push_back(r);
+    }
+    for (auto& b : outputs_) {
+        ArrayRef r = b->buf()->ref();
+        r.flags = (mode == Forwarding::Host) ? F_WRITE : 0u;
+        refs.push_back(r);
+    }
+    return refs;
+}
+
+void ClPipelineStage::run(bool initializerKernels, Forwarding mode) {
+    if (!cruncher_ || cruncher_->errorCode() != 0) return;
+    Cores& cores = *cruncher_->numberCruncher();
+    auto refs = parameterRefs(mode);
+    if (refs.empty()) {
+        fprintf(stderr, "no buffer found.\n");
+        return;
+    }
+    const auto& list = initializerKernels ? initKernels_ : kernels_;
+    const size_t n = list.size();
+    for (size_t i = 0; i < n; i++) {
+        std::vector<ArrayRef> r = refs;
+        if (mode == Forwarding::Host && n > 1) {
+            // inputs are uploaded by the first kernel only, outputs downloaded by the last one only (ClPipeline.cs:421-520)
+            const size_t nin = inputs_.size(), nout = outputs_.size();
+            if (i > 0)
+                for (size_t j = 0; j < nin; j++) r[j].flags = 0u;
+            if (i + 1 < n)
+                for (size_t j = 0; j < nout; j++) r[r.size() - nout + j].flags = 0u;
+        }
+        const int computeId = initializerKernels ? (int)(1000000 + i) : (int)(i + 1);
+        cores.compute({list[i].name}, cruncher_->repeatCount, std::string(), r, list[i].globalRange, computeId, 0, false, 4,
+                      Cores::PIPELINE_EVENT, list[i].localRange);
+    }
+    if (initializerKernels) cruncher_->sync();
+}
+
+// ------------------------------------------------------------------ pipeline
+int ClPipeline::errorCode() const {
+    int e = 0;
+    for (auto* s : stages_) e += s->errorCode();
+    return e;
+}
+std::string ClPipeline::errorMessage() const {
+    std::string m;
+    for (auto* s : stages_) m += s->errorMessage();
+    return m;
+}
+
+bool ClPipeline::pushData(const std::vector<void*>& data, const std::vector<void*>& popResultsHere) {
+    const int S = (int)stages_.size();
+    if (S == 0 || errorCode() != 0) {
+        fprintf(stderr, "Zero pipeline stages or a stage failed to build.\n%s\n", errorMessage().c_str());
+        return false;
+    }
+    const bool hasData = !data.empty(), hasPop = !popResultsHere.empty();
+
+    // 1) every stage computes on its `buf`s — enqueued without host synchronisation, so all devices run concurrently
+    for (auto* s : stages_) {
+        s->cruncher_->setEnqueueMode(true);
+        s->run(false, mode_);
+    }
+
+    // 2) meanwhile, every stage's previous results move on: duplicate output(stage k) → duplicate input(stage k+1)
+    for (int k = 0; k < S; k++) {
+        ClPipelineStage* s = stages_[k];
+        if (k == 0 && hasData) {
+            for (size_t j = 0; j < s->inputs_.size() && j < data.size(); j++) {
+                ClArray* dst = s->inputs_[j]->bufDuplicate();
+                if (mode_ == Forwarding::PeerToPeer) {
+                    ck_handle b = s->cruncher_->numberCruncher()->worker(0).buffer(dst->ref());
+                    writeToBuffer(s->forwardQueue_, b, data[j]);
+                } else {
+                    memcpy(dst->data(), data[j], (size_t)(dst->Length() * dst->elementSize()));
+                }
+            }
+        }
+        if (k + 1 < S) {
+            ClPipelineStage* nx = stages_[k + 1];
+            for (size_t j = 0; j < s->outputs_.size() && j < nx->inputs_.size(); j++) {
+                ClArray* src = s->outputs_[j]->bufDuplicate();
+                ClArray* dst = nx->inputs_[j]->bufDuplicate();
+                const int64_t n = std::min(src->Length(), dst->Length());
+                if (mode_ == Forwarding::PeerToPeer) {
+                    ck_handle sb = s->cruncher_->numberCruncher()->worker(0).buffer(src->ref());
+                    ck_handle db = nx->cruncher_->numberCruncher()->worker(0).buffer(dst->ref());
+                    ckCopyBufferPeer(nx->forwardQueue_, db, sb, 0, (int32_t)n, nullptr, nullptr);  // NVLink, no host bounce
+                } else {
+                    memcpy(dst->data(), src->data(), (size_t)(n * src->elementSize()));
+                }
+            }
+        } else if (hasPop) {
+            for (size_t j = 0; j < s->outputs_.size() && j < popResultsHere.size(); j++) {
+                ClArray* src = s->outputs_[j]->bufDuplicate();
+                if (mode_ == Forwarding::PeerToPeer) {
+                    ck_handle b = s->cruncher_->numberCruncher()->worker(0).buffer(src->ref());
+                    readFromBuffer(s->forwardQueue_, b, popResultsHere[j]);
+                } else {
+                    memcpy(popResultsHere[j], src->data(), (size_t)(src->Length() * src->elementSize()));
+                }
+            }
+        }
+    }
+
+    // 3) join: all computes and all hand-offs of this push
+    for (auto* s : stages_) {
+        s->cruncher_->setEnqueueMode(false);  // drains the queues the stage used
+        finish(s->forwardQueue_);
+    }
+
+    // 4) switch duplicates with real buffers (ClPipeline.cs:87-111)
+    for (int i = 0; i < S; i++) {
+        if (hasData || i != 0)
+            for (auto& b : stages_[i]->inputs_) b->switchBuffers();
+        if (hasPop || i != S - 1)
+            for (auto& b : stages_[i]->outputs_) b->switchBuffers();
+    }
+
+    counter++;
+    if ((counter > (S * 2 - 2)) && !hasData && !hasPop) return true;
+    if ((counter > (S * 2 - 1)) && hasData && !hasPop) return true;
+    if ((counter > (S * 2 - 1)) && !hasData && hasPop) return true;
+    if ((counter > (S * 2)) && hasData && hasPop) return true;
+    return false;
+}
+
+}  // namespace cekirdekler

@@ -1,0 +1,107 @@
+// pipeline.h — device-to-device stage pipeline (ClPipeline / ClPipelineStage / ClPipelineStageBuffer).
+//
+// B200-native restatement of the reference's Pipeline namespace (ClPipeline.cs:41-2356).  Each stage owns a
+// ClNumberCruncher on its own device(s) and double-buffered inputs/outputs (`buf` / `bufDuplicate`); one
+// pushData() runs every stage on its `buf`s while, concurrently, every stage's previous results (`bufDuplicate`)
+// move to the next stage's input duplicate; then all pairs swap (ClPipeline.cs:49-125, :2177-2208).
+// Results therefore appear after 2S-2 .. 2S pushes exactly as in the reference (:114-124).
+//
+// What changes is where the bytes travel.  The reference downloads every stage's outputs to host arrays, memcpy's them
+// into the next stage's host arrays and uploads them again (ClPipeline.cs:1422-1574): two host-link crossings and a
+// host copy per hand-off.  Here (Forwarding::PeerToPeer, the default) the stage buffers stay in HBM: kernels run on
+// device-resident buffers with no transfers, and a hand-off is one ckCopyBufferPeer over NVLink from stage k's output
+// duplicate into stage k+1's input duplicate.  Only the two ends touch the host: pushData's `data` arrays are uploaded
+// into stage 0's input duplicates, and the last stage's output duplicates are downloaded into `popResultsHere`.
+// Forwarding::Host keeps the reference's data path (for comparison and for parity tests).
+#pragma once
+#include "cruncher.h"
+
+#include <memory>
+#include <string>
+#include <vector>
+
+namespace cekirdekler {
+
+enum class Forwarding { PeerToPeer = 0, Host = 1 };
+
+class ClPipelineStageBuffer {  // ClPipeline.cs:1886-2356
+  public:
+    ClPipelineStageBuffer(int arrType, int64_t n, int elementsPerWorkItem);
+    ClArray* buf() const { return cur_; }
+    ClArray* bufDuplicate() const { return dup_; }
+    void switchBuffers() { std::swap(cur_, dup_); }  // ClPipeline.cs:2177-2208
+    int64_t length() const { return a_->Length(); }
+    int arrType() const { return a_->arrType(); }
+
+  private:
+    std::unique_ptr<ClArray> a_, b_;
+    ClArray* cur_;
+    ClArray* dup_;
+};
+
+class ClPipeline;
+
+class ClPipelineStage {  // ClPipeline.cs:146-1873
+  public:
+    explicit ClPipelineStage(bool debugLog = false) : debug_(debugLog) {}
+    ~ClPipelineStage();
+
+    void addDevices(const std::vector<int>& deviceOrdinals) { devices_ = deviceOrdinals; }                       // :1731
+    void addKernels(const std::string& kernels, const std::string& kernelNames, const std::vector<int>& globalRanges,
+                    const std::vector<int>& localRanges);                                                          // :1744
+    void initializerKernel(const std::string& kernelNames, const std::vector<int>& globalRanges,
+                           const std::vector<int>& localRanges);                                                   // :1678
+    ClPipelineStageBuffer* addInputBuffer(int arrType, int64_t n, int elementsPerWorkItem = 1);                   // :1810-1843
+    ClPipelineStageBuffer* addOutputBuffer(int arrType, int64_t n, int elementsPerWorkItem = 1);                  // :1845-1878
+    ClPipelineStageBuffer* addHiddenBuffer(int arrType, int64_t n, int elementsPerWorkItem = 1);                  // :1777-1808
+    void prependToStage(ClPipelineStage* stage);  // this stage runs BEFORE `stage`                                // :1704
+    void appendToStage(ClPipelineStage* stage);   // this stage runs AFTER `stage`                                 // :1717
+    ClPipeline* makePipeline(Forwarding mode = Forwarding::PeerToPeer);                                            // :1582
+    bool enqueueMode = false;
+
+    int errorCode() const { return cruncher_ ? cruncher_->errorCode() : initError_; }
+    std::string errorMessage() const { return cruncher_ ? cruncher_->errorMessage() : initMessage_; }
+    double elapsedTime = 0.0;  // ms of the last run() (device span)
+
+  private:
+    friend class ClPipeline;
+    struct KernelParameters { std::string name; int globalRange; int localRange; };
+    bool init(Forwarding mode);
+    void run(bool initializerKernels, Forwarding mode);
+    std::vector<ArrayRef> parameterRefs(Forwarding mode) const;  // inputs, hidden, outputs (ClPipeline.cs:281-370)
+
+    std::vector<int> devices_;
+    std::string kernelsToCompile_;
+    std::vector<KernelParameters> kernels_, initKernels_;
+    std::vector<std::unique_ptr<ClPipelineStageBuffer>> inputs_, outputs_, hiddens_;
+    ClPipelineStage* previous_ = nullptr;
+    ClPipelineStage* next_ = nullptr;
+    std::unique_ptr<ClNumberCruncher> cruncher_;
+    bool initComplete_ = false;
+    bool initKernelsDone_ = false;
+    int initError_ = 0;
+    std::string initMessage_;
+    bool debug_;
+    ck_handle forwardQueue_ = nullptr;  // a queue on this stage's device used for incoming hand-offs
+    ck_handle forwardCtx_ = nullptr, forwardDev_ = nullptr, forwardPlat_ = nullptr;
+};
+
+class ClPipeline {  // ClPipeline.cs:41-139
+  public:
+    ~ClPipeline() {}
+    // data / popResultsHere: host arrays (one per input of the first stage / output of the last stage), or empty.
+    // Returns true once the results delivered by this push are valid (ClPipeline.cs:114-124).
+    bool pushData(const std::vector<void*>& data = {}, const std::vector<void*>& popResultsHere = {});
+    int numberOfStages() const { return (int)stages_.size(); }
+    int counter = 0;
+    int errorCode() const;
+    std::string errorMessage() const;
+    Forwarding forwarding() const { return mode_; }
+
+  private:
+    friend class ClPipelineStage;
+    std::vector<ClPipelineStage*> stages_;
+    Forwarding mode_ = Forwarding::PeerToPeer;
+};
+
+}  // namespace cekirdekler

@@ -16,8 +16,10 @@ _PRELUDE = Path(__file__).resolve().parent / "csrc" / "shim" / "ck_prelude.cuh"
 
 
 def source(name: str) -> str:
-    """Kernel source by file stem: 'mandelbrot', 'stream', 'nbody', 'image'."""
-    return (_DIR / f"{name}.cu").read_text()
+    """Kernel source by file stem: 'mandelbrot', 'stream', 'nbody', 'image'.  A leading #line directive names the real
+    file, so NVRTC's -lineinfo (and therefore ncu's source page) maps SASS back to csrc/kernels/<name>.cu."""
+    path = _DIR / f"{name}.cu"
+    return f'#line 1 "{path}"\n' + path.read_text()
 
 
 def all_sources() -> dict:

@@ -93,6 +93,31 @@ void         ckh_balancer_step(ckh_balancer b, const double* benchmarkMs, int32_
 void         ckh_load_balance(const double* benchmarkMs, int32_t smooth, double* history, int32_t totalRange, int32_t* ranges,
                               int32_t step, int32_t devices);
 
+/* ---- Pipeline.ClPipeline / ClPipelineStage ---------------------------- ClPipeline.cs:41-2356 */
+typedef void* ckh_stage;     /* ClPipelineStage */
+typedef void* ckh_pipeline;  /* ClPipeline */
+ckh_stage    ckh_stage_create(int32_t debugLog);                                                         /* :176 */
+void         ckh_stage_destroy(ckh_stage s);
+void         ckh_stage_add_devices(ckh_stage s, const int32_t* deviceOrdinals, int32_t n);               /* :1731 */
+void         ckh_stage_add_kernels(ckh_stage s, const char* kernels, const char* kernelNames, const int32_t* globalRanges,
+                                   const int32_t* localRanges, int32_t n);                               /* :1744 */
+void         ckh_stage_initializer_kernel(ckh_stage s, const char* kernelNames, const int32_t* globalRanges,
+                                          const int32_t* localRanges, int32_t n);                        /* :1678 */
+/* role: 0 input (:1810), 1 output (:1845), 2 hidden (:1777); the stage allocates `buf` and `bufDuplicate` */
+void         ckh_stage_add_buffer(ckh_stage s, int32_t role, int32_t arrType, int64_t n, int32_t elementsPerWorkItem);
+void         ckh_stage_prepend_to(ckh_stage s, ckh_stage other);   /* s runs before other  (:1704) */
+void         ckh_stage_append_to(ckh_stage s, ckh_stage other);    /* s runs after other   (:1717) */
+void         ckh_stage_set_enqueue_mode(ckh_stage s, int32_t v);
+/* hostForwarding = 0: hand-offs are NVLink peer copies between device buffers; 1: the reference's host bounce (:1422-1574) */
+ckh_pipeline ckh_stage_make_pipeline(ckh_stage s, int32_t hostForwarding);                               /* :1582 */
+void         ckh_pipeline_destroy(ckh_pipeline p);
+/* pushData(data, popResultsHere) (:49-125): host arrays or NULL/0; returns 1 once the delivered results are valid */
+int32_t      ckh_pipeline_push(ckh_pipeline p, void** data, int32_t nData, void** popResultsHere, int32_t nResults);
+int32_t      ckh_pipeline_error_code(ckh_pipeline p);
+const char*  ckh_pipeline_error_message(ckh_pipeline p);
+int32_t      ckh_pipeline_forwarding(ckh_pipeline p);   /* 0 peer-to-peer, 1 host */
+int32_t      ckh_pipeline_counter(ckh_pipeline p);
+
 #ifdef __cplusplus
 }
 #endif

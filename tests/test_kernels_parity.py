@@ -221,6 +221,7 @@ def test_nbody2d_golden(gpus):
     cr = ck.ClNumberCruncher(gpu0(), kernels.source("nbody"))
     fx, fy, nn = ck.ClFloatArray(n), ck.ClFloatArray(n), ck.ClIntArray(1)
     nn[0] = n
+    nn.readOnly = True
     xc, yc = ck.ClArray(x), ck.ClArray(y)
     assert xc.nextParam(yc, fx, fy, nn).compute(cr, 1, "nBody2D", n, 256) == 0
     assert sha(fx.view) == g["sha256_fx"]
