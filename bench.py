@@ -236,14 +236,14 @@ def bench_nbody(ck, kernels, po, devs, pk, sms, steps, warmup, spmd_attach=None)
     params.readOnly = True
     vel.partialRead, vel.read = True, False
     for a in (pa, pb, vel):
-        a.numberOfElementsPerWorkItem = 4
+        a.numberOfElementsPerWorkItem = 4   # one work-item = one body
     src, dst = pa, pb
     ts_wall, ts_dev = [], []
     for i in range(warmup + steps):
         src.read, src.partialRead, src.write = True, False, False
         dst.read, dst.partialRead, dst.write = False, False, True
         t0 = time.perf_counter()
-        assert src.nextParam(vel, dst, params).compute(cr, 1, "nBody3D", n, 256) == 0
+        assert src.nextParam(vel, dst, params).compute(cr, 1, "nBody3D", n, 128) == 0
         if i >= warmup:
             ts_wall.append(time.perf_counter() - t0)
             ts_dev.append(max(cr.benchmarks(1)) * 1e-3)
@@ -467,9 +467,24 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--balancer", default="adaptive", choices=["adaptive", "reference"])
     ap.add_argument("--no-all", dest="all", action="store_false", help="skip the SAXPY and n-body workloads")
+    ap.add_argument("--only", default=None, choices=["nbody", "saxpy"],
+                    help="profiling aid: run just this secondary workload on one GPU and print its numbers")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
-    if args.impl == "reference":
+    if args.only:
+        import cekirdekler_b200 as ck
+        from cekirdekler_b200 import kernels
+        from cekirdekler_b200._native import host, shim
+        from oracle import pyoracle as po
+
+        dev = ck.ClPlatforms.all().gpus()[0]
+        pk = peaks()
+        if args.only == "nbody":
+            out = bench_nbody(ck, kernels, po, dev, pk, host().ckh_gpu_compute_units(0), args.steps, args.warmup)
+        else:
+            out = bench_saxpy(ck, kernels, dev, shim(), pk, args.steps, args.warmup)
+        print(json.dumps({"workload": args.only, **out}))
+    elif args.impl == "reference":
         run_reference(args)
     else:
         run_ours(args)

@@ -155,7 +155,27 @@ def host() -> C.CDLL:
             "ckh_pipeline_push": (i32, [vp, C.POINTER(vp), i32, C.POINTER(vp), i32]),
             "ckh_pipeline_error_code": (i32, [vp]), "ckh_pipeline_error_message": (cp, [vp]),
             "ckh_pipeline_forwarding": (i32, [vp]), "ckh_pipeline_counter": (i32, [vp]),
+            "ckh_dparray_wrap": (vp, [i32, vp]), "ckh_dparray_create": (vp, [i32, i32, i64, i32]),
+            "ckh_dparray_destroy": (None, [vp]),
+            "ckh_dpstage_create": (vp, [cp, i32, i32]), "ckh_dpstage_destroy": (None, [vp]),
+            "ckh_dpstage_bind_array": (None, [vp, vp]), "ckh_dpstage_stop_transmission": (None, [vp, i32]),
+            "ckh_dpipeline_create": (vp, [i32, cp, i32]), "ckh_dpipeline_destroy": (None, [vp]),
+            "ckh_dpipeline_add_stage": (None, [vp, vp]), "ckh_dpipeline_feed": (None, [vp]),
+            "ckh_dpipeline_feed_async_begin": (None, [vp]), "ckh_dpipeline_feed_async_end": (None, [vp]),
+            "ckh_dpipeline_set_serial": (None, [vp, i32]), "ckh_dpipeline_error_code": (i32, [vp]),
+            "ckh_dpipeline_error_message": (cp, [vp]), "ckh_dpipeline_latency": (i32, [vp]),
+            "ckh_task_create": (vp, [C.POINTER(vp), i32, C.POINTER(cp), pi32, i32, cp, i32, i32, i32, i32, i32, i32]),
+            "ckh_task_destroy": (None, [vp]), "ckh_task_set_type": (None, [vp, i32]), "ckh_task_get_type": (i32, [vp]),
+            "ckh_task_set_callback": (None, [vp, vp, vp]), "ckh_task_compute": (i32, [vp, vp]),
+            "ckh_taskpool_create": (vp, []), "ckh_taskpool_destroy": (None, [vp]), "ckh_taskpool_feed": (None, [vp, vp]),
+            "ckh_taskpool_reset": (None, [vp]), "ckh_taskpool_remaining": (i32, [vp]),
+            "ckh_devicepool_create": (vp, [i32, cp, i32, i32]), "ckh_devicepool_destroy": (None, [vp]),
+            "ckh_devicepool_add_device": (None, [vp, i32]), "ckh_devicepool_enqueue": (None, [vp, vp]),
+            "ckh_devicepool_finish": (dbl, [vp]), "ckh_devicepool_dispose": (None, [vp]),
+            "ckh_devicepool_error_code": (i32, [vp]), "ckh_devicepool_error_message": (cp, [vp]),
+            "ckh_devicepool_tasks_per_device": (i32, [vp, pi32, i32]),
         }
+        L.CALLBACK_FN = C.CFUNCTYPE(None, vp)
         for name, (res, args) in sig.items():
             fn = getattr(L, name)
             fn.restype = res

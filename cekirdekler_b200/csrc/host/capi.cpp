@@ -274,6 +274,7 @@ void ckh_load_balance(const double* benchMs, int32_t smooth, double* history, in
 
 // ------------------------------------------------------------------ device-to-device pipeline (ClPipeline.cs:41-2356)
 #include "pipeline.h"
+#include "pool.h"
 
 extern "C" {
 
@@ -311,5 +312,97 @@ int32_t ckh_pipeline_error_code(ckh_pipeline p) { return p ? static_cast<ClPipel
 const char* ckh_pipeline_error_message(ckh_pipeline p) { return keep(p ? static_cast<ClPipeline*>(p)->errorMessage() : "null pipeline"); }
 int32_t ckh_pipeline_forwarding(ckh_pipeline p) { return p ? (int32_t)static_cast<ClPipeline*>(p)->forwarding() : -1; }
 int32_t ckh_pipeline_counter(ckh_pipeline p) { return p ? static_cast<ClPipeline*>(p)->counter : 0; }
+
+// ---- SingleGPUPipeline (ClPipeline.cs:2357-3240)
+ckh_dparray ckh_dparray_wrap(int32_t type, ckh_array userArray) {
+    if (!userArray) return nullptr;
+    return new DevicePipelineArray((DevicePipelineArrayType)type, static_cast<ClArray*>(userArray));
+}
+ckh_dparray ckh_dparray_create(int32_t type, int32_t arrType, int64_t n, int32_t elementsPerWorkItem) {
+    return new DevicePipelineArray((DevicePipelineArrayType)type, arrType, n, elementsPerWorkItem);
+}
+void ckh_dparray_destroy(ckh_dparray a) { delete static_cast<DevicePipelineArray*>(a); }
+ckh_dpstage ckh_dpstage_create(const char* kernelNames, int32_t globalRange, int32_t localRange) {
+    return new DevicePipelineStage(kernelNames ? kernelNames : "", globalRange, localRange);
+}
+void ckh_dpstage_destroy(ckh_dpstage s) { delete static_cast<DevicePipelineStage*>(s); }
+void ckh_dpstage_bind_array(ckh_dpstage s, ckh_dparray a) {
+    if (s && a) static_cast<DevicePipelineStage*>(s)->bindArray(static_cast<DevicePipelineArray*>(a));
+}
+void ckh_dpstage_stop_transmission(ckh_dpstage s, int32_t v) {
+    if (s) static_cast<DevicePipelineStage*>(s)->stopHostDeviceTransmission = (v != 0);
+}
+ckh_dpipeline ckh_dpipeline_create(int32_t deviceOrdinal, const char* kernelCodes, int32_t computeQueueConcurrency) {
+    return new DevicePipeline(deviceOrdinal, kernelCodes ? kernelCodes : "", computeQueueConcurrency > 0 ? computeQueueConcurrency : 16);
+}
+void ckh_dpipeline_destroy(ckh_dpipeline p) { delete static_cast<DevicePipeline*>(p); }
+#define DP(p) (*static_cast<DevicePipeline*>(p))
+void ckh_dpipeline_add_stage(ckh_dpipeline p, ckh_dpstage s) { if (p && s) DP(p).addStage(static_cast<DevicePipelineStage*>(s)); }
+void ckh_dpipeline_feed(ckh_dpipeline p) { if (p) DP(p).feed(); }
+void ckh_dpipeline_feed_async_begin(ckh_dpipeline p) { if (p) DP(p).feedAsyncBegin(); }
+void ckh_dpipeline_feed_async_end(ckh_dpipeline p) { if (p) DP(p).feedAsyncEnd(); }
+void ckh_dpipeline_set_serial(ckh_dpipeline p, int32_t serial) {
+    if (!p) return;
+    if (serial) DP(p).enableSerialMode();
+    else DP(p).enableParallelMode();
+}
+int32_t ckh_dpipeline_error_code(ckh_dpipeline p) { return p ? DP(p).errorCode() : 1; }
+const char* ckh_dpipeline_error_message(ckh_dpipeline p) { return keep(p ? DP(p).errorMessage() : "null pipeline"); }
+int32_t ckh_dpipeline_latency(ckh_dpipeline p) { return p ? DP(p).latency() : 0; }
+
+// ---- Pool: ClTask / ClTaskPool / ClDevicePool (ClPipeline.cs:3241-5078)
+ckh_task ckh_task_create(ckh_array* arrays, int32_t nArrays, const char** readWrite, const int32_t* elems, int32_t computeId,
+                         const char* kernelNames, int32_t globalRange, int32_t localRange, int32_t offset, int32_t pipeline,
+                         int32_t pipelineType, int32_t blobs) {
+    auto* t = new ClTask();
+    for (int i = 0; i < nArrays; i++) {
+        ClArray* a = static_cast<ClArray*>(arrays[i]);
+        t->arrays.push_back(a);
+        // ClArray.task() freezes the flags at creation time (ClArray.cs:1552-1583)
+        t->readWrite.push_back(readWrite && readWrite[i] ? std::string(readWrite[i]) : a->flagString());
+        t->elementsPerItem.push_back(elems ? elems[i] : a->numberOfElementsPerWorkItem);
+    }
+    t->computeId = computeId;
+    t->kernelNamesString = kernelNames ? kernelNames : "";
+    t->globalRange = globalRange;
+    t->localRange = localRange;
+    t->ofsetGlobalRange = offset;
+    t->pipeline = pipeline != 0;
+    t->pipelineType = pipelineType != 0;
+    t->pipelineBlobs = blobs;
+    return t;
+}
+void ckh_task_destroy(ckh_task t) { delete static_cast<ClTask*>(t); }
+void ckh_task_set_type(ckh_task t, int32_t type) { if (t) static_cast<ClTask*>(t)->type = type; }
+int32_t ckh_task_get_type(ckh_task t) { return t ? static_cast<ClTask*>(t)->type : 0; }
+void ckh_task_set_callback(ckh_task t, ckh_callback_fn fn, void* user) {
+    if (!t) return;
+    if (fn) static_cast<ClTask*>(t)->callback = [fn, user] { fn(user); };
+    else static_cast<ClTask*>(t)->callback = nullptr;
+}
+int32_t ckh_task_compute(ckh_task t, ckh_cruncher c) { return (t && c) ? static_cast<ClTask*>(t)->compute(CR(c)) : -1; }
+
+ckh_taskpool ckh_taskpool_create(void) { return new ClTaskPool(); }
+void ckh_taskpool_destroy(ckh_taskpool p) { delete static_cast<ClTaskPool*>(p); }
+void ckh_taskpool_feed(ckh_taskpool p, ckh_task t) { if (p && t) static_cast<ClTaskPool*>(p)->feed(*static_cast<ClTask*>(t)); }
+void ckh_taskpool_reset(ckh_taskpool p) { if (p) static_cast<ClTaskPool*>(p)->reset(); }
+int32_t ckh_taskpool_remaining(ckh_taskpool p) { return p ? static_cast<ClTaskPool*>(p)->remainingTaskGroupsOrTasks() : 0; }
+
+ckh_devicepool ckh_devicepool_create(int32_t poolType, const char* kernelCode, int32_t fineGrained, int32_t maxQueuesPerDevice) {
+    return new ClDevicePool(poolType ? DEVICE_ROUND_ROBIN : DEVICE_COMPUTE_AT_WILL, kernelCode ? kernelCode : "", fineGrained != 0,
+                            maxQueuesPerDevice > 0 ? maxQueuesPerDevice : 3);
+}
+void ckh_devicepool_destroy(ckh_devicepool p) { delete static_cast<ClDevicePool*>(p); }
+#define POOL(p) (*static_cast<ClDevicePool*>(p))
+void ckh_devicepool_add_device(ckh_devicepool p, int32_t ordinal) { if (p) POOL(p).addDevice(ordinal); }
+void ckh_devicepool_enqueue(ckh_devicepool p, ckh_taskpool tp) { if (p && tp) POOL(p).enqueueTaskPool(*static_cast<ClTaskPool*>(tp)); }
+double ckh_devicepool_finish(ckh_devicepool p) { return p ? POOL(p).finish() : 0.0; }
+void ckh_devicepool_dispose(ckh_devicepool p) { if (p) POOL(p).dispose(); }
+int32_t ckh_devicepool_error_code(ckh_devicepool p) { return p ? POOL(p).errorCode() : 1; }
+const char* ckh_devicepool_error_message(ckh_devicepool p) { return keep(p ? POOL(p).errorMessage() : "null pool"); }
+int32_t ckh_devicepool_tasks_per_device(ckh_devicepool p, int32_t* out, int32_t n) {
+    if (!p) return 0;
+    return copy_out(POOL(p).tasksPerDevice(), out, n);
+}
 
 }  // extern "C"

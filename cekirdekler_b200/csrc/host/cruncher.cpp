@@ -201,8 +201,13 @@ int ClParameterGroup::compute(ClNumberCruncher& cr, int computeId, const std::st
     }
     auto kernels = splitKernelNames(kernelNamesString);
     if (kernels.empty()) return complain(9, "Kernel-name error: no kernel names given.");
+    int launchErrorsBefore = 0;
+    for (int i = 0; i < cores.numberOfDevices(); i++) launchErrorsBefore += cores.worker(i).launchErrors();
     cores.compute(kernels, cr.repeatCount, cr.repeatCount > 1 ? cr.repeatKernelName : std::string(), refs, globalRange, computeId,
                   ofsetGlobalRange, pipeline, pipelineBlobs, pipelineType, localRange);
+    int launchErrorsAfter = 0;
+    for (int i = 0; i < cores.numberOfDevices(); i++) launchErrorsAfter += cores.worker(i).launchErrors();
+    if (launchErrorsAfter != launchErrorsBefore) return 10;  // a kernel could not be launched (message already printed)
     if (cr.performanceFeed) {
         cr.lastComputePerformanceReport = cores.performanceReport(computeId);
         fprintf(stdout, "%s\n", cr.lastComputePerformanceReport.c_str());

@@ -120,6 +120,18 @@ bool ClPipelineStage::init(Forwarding mode) {
         initMessage_ = std::string("pipeline stage: cannot create the hand-off queue: ") + ckGetLastError();
         return false;
     }
+    if (mode == Forwarding::PeerToPeer) {
+        // The reference's stage arrays start zeroed on the host and are uploaded; device-resident stage buffers must start
+        // zeroed too (cudaMalloc does not clear), or the warm-up pushes would compute on whatever the memory held before.
+        Worker& w = cruncher_->numberCruncher()->worker(0);
+        for (auto* group : {&inputs_, &hiddens_, &outputs_})
+            for (auto& sb : *group)
+                for (ClArray* a : {sb->buf(), sb->bufDuplicate()}) {
+                    ck_handle b = w.buffer(a->ref());
+                    if (b) ckZeroBuffer(forwardQueue_, b);
+                }
+        finish(forwardQueue_);
+    }
     if (!initKernels_.empty()) run(true, mode);
     return true;
 }
@@ -259,6 +271,91 @@ bool ClPipeline::pushData(const std::vector<void*>& data, const std::vector<void
     if ((counter > (S * 2 - 1)) && !hasData && hasPop) return true;
     if ((counter > (S * 2)) && hasData && hasPop) return true;
     return false;
+}
+
+}  // namespace cekirdekler
+
+// ====================================================================================================================
+// SingleGPUPipeline (ClPipeline.cs:2357-3240)
+// ====================================================================================================================
+namespace cekirdekler {
+
+DevicePipelineArray::DevicePipelineArray(DevicePipelineArrayType t, ClArray* userArray) : type(t), user_(userArray) {}
+DevicePipelineArray::DevicePipelineArray(DevicePipelineArrayType t, int arrType, int64_t n, int e)
+    : type(t), a_(new ClArray(arrType, n)) {
+    a_->numberOfElementsPerWorkItem = e;
+    if (t == DevicePipelineArrayType::TRANSITION) {
+        b_.reset(new ClArray(arrType, n));
+        b_->numberOfElementsPerWorkItem = e;
+    }
+}
+
+DevicePipeline::DevicePipeline(int deviceOrdinal, const std::string& kernelCodes, int computeQueueConcurrency)
+    : device_(deviceOrdinal), code_(kernelCodes), concurrency_(computeQueueConcurrency) {}
+
+void DevicePipeline::addStage(DevicePipelineStage* stage) {
+    const int idx = (int)stages_.size();
+    stages_.push_back(stage);
+    for (auto* a : stage->arrays)
+        if (a->type == DevicePipelineArrayType::TRANSITION && a->producerStage < 0) a->producerStage = idx;
+}
+
+// Every stage is one ClNumberCruncher.compute() in enqueue mode on its own queue (enqueueModeAsyncEnable advances the
+// queue cursor, Cores.cs:83), carrying its own uploads (INPUT: whole `read`), kernels and downloads (OUTPUT: `write`).
+// In parallel mode stage k consumes what stage k-1 produced during the previous feed(), so all stages of one feed()
+// are independent and overlap on the device (ClPipeline.cs:2448-2536); in serial mode they run in order on one feed().
+void DevicePipeline::enqueueAll() {
+    if (!cruncher_) cruncher_.reset(new ClNumberCruncher({device_}, code_, false, concurrency_));
+    if (cruncher_->errorCode() != 0 || !cruncher_->numberCruncher()) return;
+    Cores& cores = *cruncher_->numberCruncher();
+    cores.setEnqueueMode(true);
+    for (int i = 0; i < (int)stages_.size(); i++) {
+        DevicePipelineStage& st = *stages_[i];
+        std::vector<ArrayRef> refs;
+        for (auto* a : st.arrays) {
+            int v = 0;
+            if (a->type == DevicePipelineArrayType::TRANSITION && !serialMode_)
+                v = (a->producerStage == i) ? (runCounter_ & 1) : ((runCounter_ + 1) & 1);
+            ArrayRef r = a->version(v)->ref();
+            r.flags = 0u;
+            if (!st.stopHostDeviceTransmission) {
+                if (a->type == DevicePipelineArrayType::INPUT) r.flags = F_READ;
+                if (a->type == DevicePipelineArrayType::OUTPUT) r.flags = F_WRITE;
+            }
+            refs.push_back(r);
+        }
+        if (!serialMode_) cores.setEnqueueModeAsyncEnable(true);  // next queue for this stage
+        std::vector<std::string> names;
+        {
+            std::string cur;
+            for (char c : st.kernelNames + " ") {
+                if (c == ' ' || c == ',' || c == ';' || c == '-' || c == '\n' || c == '@') {
+                    if (!cur.empty()) names.push_back(cur);
+                    cur.clear();
+                } else {
+                    cur.push_back(c);
+                }
+            }
+        }
+        cores.compute(names, 1, std::string(), refs, st.globalRange, /*computeId=*/i, 0, false, 4, Cores::PIPELINE_EVENT, st.localRange);
+        if (!serialMode_) {
+            cores.flushLastUsedCommandQueue();
+            cores.setEnqueueModeAsyncEnable(false);
+        }
+    }
+    open_ = true;
+}
+
+void DevicePipeline::feedAsyncBegin() { enqueueAll(); }
+void DevicePipeline::feedAsyncEnd() {
+    if (!open_ || !cruncher_ || !cruncher_->numberCruncher()) return;
+    cruncher_->numberCruncher()->setEnqueueMode(false);  // joins every queue used by this feed
+    open_ = false;
+    runCounter_++;
+}
+void DevicePipeline::feed() {
+    feedAsyncBegin();
+    feedAsyncEnd();
 }
 
 }  // namespace cekirdekler

@@ -105,3 +105,66 @@ class ClPipeline {  // ClPipeline.cs:41-139
 };
 
 }  // namespace cekirdekler
+
+// ====================================================================================================================
+// SingleGPUPipeline: N kernel stages overlapped on ONE device (ClPipeline.cs:2357-3240)
+// ====================================================================================================================
+namespace cekirdekler {
+
+enum class DevicePipelineArrayType { INPUT = 0, OUTPUT = 1, INTERNAL = 2, TRANSITION = 3 };  // ClPipeline.cs:3178-3184
+
+// An array bound to one or two stages.  INPUT/OUTPUT wrap the caller's host array (uploaded before / downloaded after the
+// stage's kernels, on the stage's own queue); INTERNAL lives only in HBM; TRANSITION is shared by two consecutive stages
+// and double-buffered in HBM: the producer writes one copy while the consumer reads the copy of the previous feed().
+class DevicePipelineArray {  // ClPipeline.cs:3186-3240
+  public:
+    DevicePipelineArray(DevicePipelineArrayType type, ClArray* userArray);                         // INPUT / OUTPUT
+    DevicePipelineArray(DevicePipelineArrayType type, int arrType, int64_t n, int elementsPerWorkItem = 1);  // INTERNAL / TRANSITION
+    DevicePipelineArrayType type;
+    ClArray* version(int v) const { return (v & 1) && b_ ? b_.get() : (user_ ? user_ : a_.get()); }
+    int producerStage = -1;  // first stage that bound a TRANSITION array
+
+  private:
+    ClArray* user_ = nullptr;
+    std::unique_ptr<ClArray> a_, b_;
+};
+
+class DevicePipelineStage {  // ClPipeline.cs:2636-3176
+  public:
+    DevicePipelineStage(const std::string& kernelNames, int globalRange, int localRange)
+        : kernelNames(kernelNames), globalRange(globalRange), localRange(localRange) {}
+    void bindArray(DevicePipelineArray* a) { arrays.push_back(a); }                                // :3106
+    bool stopHostDeviceTransmission = false;                                                       // :2638
+    std::string kernelNames;
+    int globalRange, localRange;
+    std::vector<DevicePipelineArray*> arrays;
+};
+
+class DevicePipeline {  // ClPipeline.cs:2359-2634
+  public:
+    DevicePipeline(int deviceOrdinal, const std::string& kernelCodes, int computeQueueConcurrency = 16);
+    void addStage(DevicePipelineStage* stage);                                                     // :2381
+    void feed();                                                                                   // :2570
+    void feedAsyncBegin();                                                                         // :2603
+    void feedAsyncEnd();                                                                           // :2616
+    void enableSerialMode() { serialMode_ = true; }                                                // :2621
+    void enableParallelMode() { serialMode_ = false; }                                             // :2625
+    int errorCode() const { return cruncher_ ? cruncher_->errorCode() : 0; }
+    std::string errorMessage() const { return cruncher_ ? cruncher_->errorMessage() : std::string(); }
+    int runCounter() const { return runCounter_; }
+    // feeds between handing an input in and its result appearing in the OUTPUT array: 0 in serial mode, stages-1 in parallel mode
+    int latency() const { return serialMode_ ? 0 : (int)stages_.size() - 1; }
+
+  private:
+    void enqueueAll();
+    int device_;
+    std::string code_;
+    int concurrency_;
+    std::vector<DevicePipelineStage*> stages_;
+    std::unique_ptr<ClNumberCruncher> cruncher_;
+    bool serialMode_ = false;
+    int runCounter_ = 0;
+    bool open_ = false;
+};
+
+}  // namespace cekirdekler

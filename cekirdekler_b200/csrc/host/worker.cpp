@@ -1,6 +1,7 @@
 // worker.cpp — see worker.h.  Reference: Worker.cs (line ranges cited per method in the header).
 #include "worker.h"
 
+#include <cstdio>
 #include <cstring>
 
 namespace cekirdekler {
@@ -291,24 +292,33 @@ int Worker::readPartialEvent(const std::vector<ArrayRef>& arrs, int reference, i
 
 int Worker::compute(const std::string& kernel, int reference, int globalRange, int localRange, int computeId, ck_handle q) {
     ck_handle k = kernelWithId(kernel, computeId);
-    return ::compute(q ? q : q_[0], k, range(reference), range(globalRange), range(localRange));
+    return noteLaunch(::compute(q ? q : q_[0], k, range(reference), range(globalRange), range(localRange)), kernel);
+}
+
+int Worker::noteLaunch(int err, const std::string& kernel) {
+    if (err) {
+        launchErrors_++;
+        lastLaunchError_ = "kernel \"" + kernel + "\" on device " + std::to_string(ordinal_) + ": " + ckGetLastError();
+        fprintf(stderr, "Cekirdekler launch error: %s\n", lastLaunchError_.c_str());
+    }
+    return err;
 }
 
 int Worker::computeRepeated(const std::string& kernel, int reference, int globalRange, int localRange, int computeId, int repeats,
                             ck_handle q) {
-    return ::computeRepeated(q ? q : q_[0], kernelWithId(kernel, computeId), range(reference), range(globalRange), range(localRange),
-                             repeats);
+    return noteLaunch(::computeRepeated(q ? q : q_[0], kernelWithId(kernel, computeId), range(reference), range(globalRange),
+                                        range(localRange), repeats), kernel);
 }
 
 int Worker::computeRepeatedWithSyncKernel(const std::string& kernel, int reference, int globalRange, int localRange, int computeId,
                                           int repeats, const std::string& syncKernel, ck_handle q) {
-    return ::computeRepeatedWithSyncKernel(q ? q : q_[0], kernelWithId(kernel, computeId), range(reference), range(globalRange),
-                                           range(localRange), repeats, kernelWithId(syncKernel, computeId), range(0));
+    return noteLaunch(::computeRepeatedWithSyncKernel(q ? q : q_[0], kernelWithId(kernel, computeId), range(reference), range(globalRange),
+                                                      range(localRange), repeats, kernelWithId(syncKernel, computeId), range(0)), kernel);
 }
 
 int Worker::computeEvent(const std::string& kernel, int reference, int globalRange, int localRange, int computeId, ck_handle waitArr,
                          ck_handle evt, ck_handle q) {
-    return ::computeEvent(q, kernelWithId(kernel, computeId), range(reference), range(globalRange), range(localRange), waitArr, evt);
+    return noteLaunch(::computeEvent(q, kernelWithId(kernel, computeId), range(reference), range(globalRange), range(localRange), waitArr, evt), kernel);
 }
 
 void Worker::startBench(bool deviceClock) {

@@ -105,10 +105,16 @@ class Worker {
     void endBench(int computeId);
     double benchmark(int computeId) const;
 
+    int launchErrors() const { return launchErrors_; }
+    const std::string& lastLaunchError() const { return lastLaunchError_; }
+
     std::mutex mu;  // the reference serialises per-worker work with lock(workers[i]) (Cores.cs:751)
 
   private:
     void fail(int code, const std::string& msg);
+    int noteLaunch(int err, const std::string& kernel);
+    int launchErrors_ = 0;
+    std::string lastLaunchError_;
 
     int ordinal_ = 0;
     bool streaming_ = false;

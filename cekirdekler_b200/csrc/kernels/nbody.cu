@@ -9,9 +9,16 @@
 //             are bit-identical to oracle_nbody2d (sqrtf and the division are IEEE-rounded on both sides).
 //   nBody3D   the BASELINE float4 step (no reference source; defined here and in oracle_nbody3d_step):
 //             a_i = sum_j m_j d / (|d|^2 + eps2)^(3/2), v += a dt, posOut = p + v dt;  params = { dt, eps2, (float)n }.
-//             One work-item = one body (numberOfElementsPerWorkItem = 4 floats on vel/posOut); pos is a whole-array
-//             `read` input (every device needs all of it: the one broadcast of the path).  The inverse square root is
-//             the raw SFU approximation (MUFU.RSQ); parity with the oracle is <= 1e-4 relative on positions.
+//             pos is a whole-array `read` input (every device needs all of it: the one broadcast of the path).  The
+//             inverse square root is the raw SFU approximation (MUFU.RSQ); parity with the oracle is <= 1e-4 relative
+//             on positions.  One work-item = one body (numberOfElementsPerWorkItem = 4 floats on vel/posOut); the
+//             work-group size must be a multiple of 64 and at least 128.  The j loop runs over PAIRS of bodies with
+//             Blackwell's packed two-lane FP32 instructions (FADD2/FMUL2/FFMA2, PTX *.f32x2): each issue slot carries
+//             two interactions.  Measured on B200 (build/exp micro-benchmark, round 1, per-SM cycles per
+//             warp-interaction): scalar 1 body/thread 17.9, packed pairs with 2 bodies/thread 15.9; the floor is 12
+//             FMA-pipe cycles (3 sub, 3 fma, 3 mul, 3 fma per interaction).  See the comment above the kernel for how
+//             the work-group divides its bodies and the j range.
+//   nBody3D1  the same step with scalar instructions and no restriction on the work-group size.
 // Work is counted as 20 FLOP per interaction.
 
 #define NB_TILE 256   // bodies staged per shared-memory tile; equals the work-group size used by the benchmarks
@@ -57,7 +64,7 @@ __kernel void nBody2D(const float* __restrict__ x, const float* __restrict__ y, 
     fy[i] = fy0;
 }
 
-__kernel void nBody3D(const float4* __restrict__ pos, float4* __restrict__ vel, float4* __restrict__ posOut,
+__kernel void nBody3D1(const float4* __restrict__ pos, float4* __restrict__ vel, float4* __restrict__ posOut,
                       const float* __restrict__ params)
 {
     __shared__ float4 tile[NB_TILE];
@@ -91,4 +98,133 @@ __kernel void nBody3D(const float4* __restrict__ pos, float4* __restrict__ vel, 
     v.z = __fmaf_rn(az, dt, v.z);
     vel[i] = v;
     posOut[i] = make_float4(__fmaf_rn(v.x, dt, pi.x), __fmaf_rn(v.y, dt, pi.y), __fmaf_rn(v.z, dt, pi.z), pi.w);
+}
+
+// ---- packed two-lane FP32 helpers (sm_100+): one instruction, two independent IEEE operations ----
+typedef unsigned long long ck_f32x2;
+__device__ __forceinline__ ck_f32x2 ck_pack(float lo, float hi) { ck_f32x2 r; asm("mov.b64 %0, {%1,%2};" : "=l"(r) : "f"(lo), "f"(hi)); return r; }
+__device__ __forceinline__ void ck_unpack(ck_f32x2 v, float& lo, float& hi) { asm("mov.b64 {%0,%1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v)); }
+__device__ __forceinline__ ck_f32x2 ck_fma2(ck_f32x2 a, ck_f32x2 b, ck_f32x2 c) { ck_f32x2 d; asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(d) : "l"(a), "l"(b), "l"(c)); return d; }
+__device__ __forceinline__ ck_f32x2 ck_mul2(ck_f32x2 a, ck_f32x2 b) { ck_f32x2 d; asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b)); return d; }
+__device__ __forceinline__ ck_f32x2 ck_sub2(ck_f32x2 a, ck_f32x2 b) { ck_f32x2 d; asm("sub.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b)); return d; }
+
+// one body i against one PAIR of bodies j: 12 packed FMA-pipe instructions + 2 MUFU for two interactions
+#define NB_PAIR_INTERACT(PIX, PIY, PIZ, AX, AY, AZ)                                          \
+    {                                                                                        \
+        const ck_f32x2 DX = ck_sub2(PX, PIX), DY = ck_sub2(PY, PIY), DZ = ck_sub2(PZ, PIZ);  \
+        const ck_f32x2 R2 = ck_fma2(DZ, DZ, ck_fma2(DY, DY, ck_fma2(DX, DX, EPS)));          \
+        float r0, r1;                                                                        \
+        ck_unpack(R2, r0, r1);                                                               \
+        const ck_f32x2 INV = ck_pack(ck_rsqrt_approx(r0), ck_rsqrt_approx(r1));              \
+        const ck_f32x2 S = ck_mul2(PM, ck_mul2(ck_mul2(INV, INV), INV));                     \
+        AX = ck_fma2(DX, S, AX);                                                             \
+        AY = ck_fma2(DY, S, AY);                                                             \
+        AZ = ck_fma2(DZ, S, AZ);                                                             \
+    }
+
+// Work decomposition inside a work-group of L work-items (L a multiple of 64; one work-item = one body, so the group owns
+// L consecutive bodies): the group is split in two halves of L/2 threads.  Thread q of either half carries the PAIR of
+// bodies (2q, 2q+1) of the group; half 0 sweeps the first half of the j tiles, half 1 the second half, and the partial
+// accelerations are combined through shared memory at the end.  Each thread therefore gets the two-bodies-per-thread
+// operand reuse (one pair of LDS.128 feeds 4 interactions) while the grid still has one thread per body — 131072 bodies
+// give 4096 warps, 6.9 per SM sub-partition, instead of 3.5 (which would both starve the schedulers and leave 13 % of
+// the SMs' time to warp-count rounding).  The next tile is prefetched into registers while the current one is consumed.
+#define NB_PREFETCH 4   // float4 loads per thread per tile: NB_TILE / (L/2) must not exceed this (L >= 128)
+
+__kernel void nBody3D(const float4* __restrict__ pos, float4* __restrict__ vel, float4* __restrict__ posOut,
+                      const float* __restrict__ params)
+{
+    // per half: a tile of NB_TILE bodies stored as NB_TILE/2 pairs, sA[p] = (x0, x1, y0, y1), sB[p] = (z0, z1, m0, m1),
+    // so one broadcast LDS.128 delivers two aligned register pairs = two packed operands
+    __shared__ float4 sA[2][NB_TILE / 2];
+    __shared__ float4 sB[2][NB_TILE / 2];
+    __shared__ float red[6][NB_TILE];       // half 1's partial accelerations (6 per thread, up to 256 threads per half)
+    const float dt = __ldg(params + 0), eps2 = __ldg(params + 1);
+    const int n = (int)__ldg(params + 2);
+    const int L2 = blockDim.x >> 1;                              // threads per half
+    const int half = (threadIdx.x >= L2) ? 1 : 0;
+    const int q = threadIdx.x - half * L2;                       // pair index inside the group
+    const int groupFirst = (int)get_global_id(0) - threadIdx.x;  // first body of this work-group
+    const int i0 = groupFirst + 2 * q, i1 = i0 + 1;
+    const float4 p0 = pos[i0], p1 = pos[i1];
+    const ck_f32x2 P0X = ck_pack(p0.x, p0.x), P0Y = ck_pack(p0.y, p0.y), P0Z = ck_pack(p0.z, p0.z);
+    const ck_f32x2 P1X = ck_pack(p1.x, p1.x), P1Y = ck_pack(p1.y, p1.y), P1Z = ck_pack(p1.z, p1.z);
+    const ck_f32x2 EPS = ck_pack(eps2, eps2);
+    ck_f32x2 AX = ck_pack(0.0f, 0.0f), AY = AX, AZ = AX, BX = AX, BY = AX, BZ = AX;
+
+    const int tiles = (n + NB_TILE - 1) / NB_TILE;
+    const int tilesPerHalf = (tiles + 1) >> 1;                   // both halves run the same trip count (barriers must match)
+    const int firstTile = half * tilesPerHalf;
+    float* fA = reinterpret_cast<float*>(sA[half]);
+    float* fB = reinterpret_cast<float*>(sB[half]);
+
+    float4 nxt[NB_PREFETCH];
+#pragma unroll
+    for (int k = 0; k < NB_PREFETCH; k++) {
+        const int t = q + k * L2;
+        const int j = firstTile * NB_TILE + t;
+        nxt[k] = (t < NB_TILE && j < n && firstTile < tiles) ? pos[j] : make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+    }
+    for (int it = 0; it < tilesPerHalf; it++) {
+        // stage the prefetched tile (padding bodies have mass 0 and contribute nothing)
+#pragma unroll
+        for (int k = 0; k < NB_PREFETCH; k++) {
+            const int t = q + k * L2;
+            if (t < NB_TILE) {
+                const int p = t >> 1, h = t & 1;
+                fA[p * 4 + h] = nxt[k].x;
+                fA[p * 4 + 2 + h] = nxt[k].y;
+                fB[p * 4 + h] = nxt[k].z;
+                fB[p * 4 + 2 + h] = nxt[k].w;
+            }
+        }
+        __syncthreads();
+        // prefetch the following tile while this one is consumed
+        const int nextTile = firstTile + it + 1;
+#pragma unroll
+        for (int k = 0; k < NB_PREFETCH; k++) {
+            const int t = q + k * L2;
+            const int j = nextTile * NB_TILE + t;
+            const bool live = (it + 1 < tilesPerHalf) && (nextTile < tiles) && (t < NB_TILE) && (j < n);
+            nxt[k] = live ? pos[j] : make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+        }
+        const float4* tA = sA[half];
+        const float4* tB = sB[half];
+#pragma unroll 2
+        for (int t = 0; t < NB_TILE / 2; t++) {
+            const float4 a = tA[t], b = tB[t];
+            const ck_f32x2 PX = ck_pack(a.x, a.y), PY = ck_pack(a.z, a.w), PZ = ck_pack(b.x, b.y), PM = ck_pack(b.z, b.w);
+            NB_PAIR_INTERACT(P0X, P0Y, P0Z, AX, AY, AZ)
+            NB_PAIR_INTERACT(P1X, P1Y, P1Z, BX, BY, BZ)
+        }
+        __syncthreads();
+    }
+    float a0x, a0y, a0z, a1x, a1y, a1z, lo, hi;
+    ck_unpack(AX, lo, hi); a0x = lo + hi;
+    ck_unpack(AY, lo, hi); a0y = lo + hi;
+    ck_unpack(AZ, lo, hi); a0z = lo + hi;
+    ck_unpack(BX, lo, hi); a1x = lo + hi;
+    ck_unpack(BY, lo, hi); a1y = lo + hi;
+    ck_unpack(BZ, lo, hi); a1z = lo + hi;
+    if (half == 1) {
+        red[0][q] = a0x; red[1][q] = a0y; red[2][q] = a0z;
+        red[3][q] = a1x; red[4][q] = a1y; red[5][q] = a1z;
+    }
+    __syncthreads();
+    if (half == 0) {
+        a0x += red[0][q]; a0y += red[1][q]; a0z += red[2][q];
+        a1x += red[3][q]; a1y += red[4][q]; a1z += red[5][q];
+        float4 v = vel[i0];
+        v.x = __fmaf_rn(a0x, dt, v.x);
+        v.y = __fmaf_rn(a0y, dt, v.y);
+        v.z = __fmaf_rn(a0z, dt, v.z);
+        vel[i0] = v;
+        posOut[i0] = make_float4(__fmaf_rn(v.x, dt, p0.x), __fmaf_rn(v.y, dt, p0.y), __fmaf_rn(v.z, dt, p0.z), p0.w);
+        v = vel[i1];
+        v.x = __fmaf_rn(a1x, dt, v.x);
+        v.y = __fmaf_rn(a1y, dt, v.y);
+        v.z = __fmaf_rn(a1z, dt, v.z);
+        vel[i1] = v;
+        posOut[i1] = make_float4(__fmaf_rn(v.x, dt, p1.x), __fmaf_rn(v.y, dt, p1.y), __fmaf_rn(v.z, dt, p1.z), p1.w);
+    }
 }

@@ -764,6 +764,8 @@ ck_handle createBuffer(ck_handle hContext, int32_t numberOfElements, int32_t clA
             delete b;
             return nullptr;
         }
+        // device-resident arrays (no read/write flag) are never uploaded: start them at zero like the host arrays they mirror
+        CK_CUDA(cudaMemset(b->dptr, 0, bytes));
     }
     b->ctx = c;
     c->retain();

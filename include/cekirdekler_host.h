@@ -118,6 +118,61 @@ const char*  ckh_pipeline_error_message(ckh_pipeline p);
 int32_t      ckh_pipeline_forwarding(ckh_pipeline p);   /* 0 peer-to-peer, 1 host */
 int32_t      ckh_pipeline_counter(ckh_pipeline p);
 
+/* ---- Pipeline.SingleGPUPipeline: stages overlapped on one device ------ ClPipeline.cs:2357-3240 */
+typedef void* ckh_dparray;    /* DevicePipelineArray */
+typedef void* ckh_dpstage;    /* DevicePipelineStage */
+typedef void* ckh_dpipeline;  /* DevicePipeline */
+/* type: DevicePipelineArrayType INPUT 0, OUTPUT 1, INTERNAL 2, TRANSITION 3 (:3178-3184) */
+ckh_dparray   ckh_dparray_wrap(int32_t type, ckh_array userArray);                                  /* INPUT / OUTPUT over a caller array */
+ckh_dparray   ckh_dparray_create(int32_t type, int32_t arrType, int64_t n, int32_t elementsPerWorkItem);  /* INTERNAL / TRANSITION */
+void          ckh_dparray_destroy(ckh_dparray a);
+ckh_dpstage   ckh_dpstage_create(const char* kernelNames, int32_t globalRange, int32_t localRange);  /* :3098 */
+void          ckh_dpstage_destroy(ckh_dpstage s);
+void          ckh_dpstage_bind_array(ckh_dpstage s, ckh_dparray a);                                  /* :3106 */
+void          ckh_dpstage_stop_transmission(ckh_dpstage s, int32_t v);                               /* :2638 */
+ckh_dpipeline ckh_dpipeline_create(int32_t deviceOrdinal, const char* kernelCodes, int32_t computeQueueConcurrency); /* :2369 */
+void          ckh_dpipeline_destroy(ckh_dpipeline p);
+void          ckh_dpipeline_add_stage(ckh_dpipeline p, ckh_dpstage s);                               /* :2381 */
+void          ckh_dpipeline_feed(ckh_dpipeline p);                                                   /* :2570 */
+void          ckh_dpipeline_feed_async_begin(ckh_dpipeline p);                                       /* :2603 */
+void          ckh_dpipeline_feed_async_end(ckh_dpipeline p);                                         /* :2616 */
+void          ckh_dpipeline_set_serial(ckh_dpipeline p, int32_t serial);                             /* :2621-2628 */
+int32_t       ckh_dpipeline_error_code(ckh_dpipeline p);
+const char*   ckh_dpipeline_error_message(ckh_dpipeline p);
+int32_t       ckh_dpipeline_latency(ckh_dpipeline p);   /* feeds between an input and its result: 0 serial, stages-1 parallel */
+
+/* ---- Pipeline.Pool: ClTask / ClTaskPool / ClDevicePool ----------------- ClPipeline.cs:3241-5078 */
+typedef void* ckh_task;        /* ClTask */
+typedef void* ckh_taskpool;    /* ClTaskPool */
+typedef void* ckh_devicepool;  /* ClDevicePool */
+typedef void (*ckh_callback_fn)(void* user);
+/* ClArray.task()/ClParameterGroup.task() (ClArray.cs:515-521, :1552-1583): freezes a compute() call; readWrite/elems may be
+ * NULL (then the arrays' current flags are frozen) */
+ckh_task     ckh_task_create(ckh_array* arrays, int32_t nArrays, const char** readWrite, const int32_t* elementsPerItem,
+                             int32_t computeId, const char* kernelNamesString, int32_t globalRange, int32_t localRange,
+                             int32_t ofsetGlobalRange, int32_t pipeline, int32_t pipelineType, int32_t pipelineBlobs);
+void         ckh_task_destroy(ckh_task t);
+void         ckh_task_set_type(ckh_task t, int32_t clTaskTypeBits);      /* ClTaskType bit flags, :3247-3321 */
+int32_t      ckh_task_get_type(ckh_task t);
+void         ckh_task_set_callback(ckh_task t, ckh_callback_fn fn, void* user);   /* :3481 */
+int32_t      ckh_task_compute(ckh_task t, ckh_cruncher c);               /* :3359 */
+ckh_taskpool ckh_taskpool_create(void);
+void         ckh_taskpool_destroy(ckh_taskpool p);
+void         ckh_taskpool_feed(ckh_taskpool p, ckh_task t);              /* :3649 (the task is copied) */
+void         ckh_taskpool_reset(ckh_taskpool p);                         /* :3642 */
+int32_t      ckh_taskpool_remaining(ckh_taskpool p);                     /* :3758 */
+/* poolType: 0 DEVICE_COMPUTE_AT_WILL, 1 DEVICE_ROUND_ROBIN (:3802-3808) */
+ckh_devicepool ckh_devicepool_create(int32_t poolType, const char* kernelCodeToCompile, int32_t fineGrainedQueueControl,
+                                     int32_t maxQueuesPerDevice);        /* :3935 */
+void         ckh_devicepool_destroy(ckh_devicepool p);
+void         ckh_devicepool_add_device(ckh_devicepool p, int32_t deviceOrdinal);   /* :4340 */
+void         ckh_devicepool_enqueue(ckh_devicepool p, ckh_taskpool pool);          /* :4400 */
+double       ckh_devicepool_finish(ckh_devicepool p);                    /* :4470, elapsed ms */
+void         ckh_devicepool_dispose(ckh_devicepool p);                   /* :4527 */
+int32_t      ckh_devicepool_error_code(ckh_devicepool p);
+const char*  ckh_devicepool_error_message(ckh_devicepool p);
+int32_t      ckh_devicepool_tasks_per_device(ckh_devicepool p, int32_t* out, int32_t n);
+
 #ifdef __cplusplus
 }
 #endif

@@ -59,7 +59,7 @@ def test_three_stage_pipeline_histograms_are_exact(gpus, host_forwarding):
         out[p] = __fsqrt_rn(__fmaf_rn(gx, gx, __fmul_rn(gy, gy)));
     }""", "sobelStage", [n], [256])
     sob.addInputBuffers((np.float32, n), (np.int32, 2))
-    sob.addOutputBuffers((np.float32, n, 16))
+    sob.addOutputBuffers((np.float32, n))               # written one pixel per work-item
     sob.appendToStage(blur)
     hist = ClPipelineStage()
     hist.addDevices(d(2))
