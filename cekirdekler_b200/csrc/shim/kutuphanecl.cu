@@ -261,7 +261,10 @@ static void transfer(void* hq, void* hb, int64_t ref, int64_t range, void* host,
         range = b->elems;
     }
     if (ref < 0 || ref + range > b->elems) {
-        set_error("transfer: element range outside the buffer");
+        // the reference would overrun the buffer here; refuse and say so (the caller ignores the return value)
+        set_error("transfer: element range [" + std::to_string(ref) + ", " + std::to_string(ref + range) + ") outside a buffer of " +
+                  std::to_string(b->elems) + " elements — nothing copied");
+        fprintf(stderr, "[KutuphaneCL] %s\n", t_last_error.c_str());
     } else if (!b->zero_copy && range > 0) {
         if (!host) {
             set_error("transfer: null host array");
