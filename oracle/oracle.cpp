@@ -33,6 +33,14 @@ int oracle_threads(void) {
 #endif
 }
 
+void oracle_set_threads(int n) {
+#ifdef _OPENMP
+    if (n > 0) omp_set_num_threads(n);
+#else
+    (void)n;
+#endif
+}
+
 // ---------------------------------------------------------------- K6: copy (Tester.cs:35-38)
 // __kernel void test(__global T* data, __global T* data2){ int id=get_global_id(0); data2[id]=data[id]; }
 void oracle_copy(const void* data, void* data2, long long offset, long long count, int elemSize) {

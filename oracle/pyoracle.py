@@ -32,6 +32,7 @@ def lib() -> C.CDLL:
         L = C.CDLL(str(build()))
         vp, ll, i32 = C.c_void_p, C.c_longlong, C.c_int
         L.oracle_threads.restype = i32
+        L.oracle_set_threads.argtypes = [i32]
         L.oracle_copy.argtypes = [vp, vp, ll, ll, i32]
         L.oracle_vector_add.argtypes = [vp, vp, vp, ll, ll]
         L.oracle_saxpy.argtypes = [vp, vp, vp, ll, ll]
@@ -54,6 +55,15 @@ def _p(a: np.ndarray):
 
 def threads() -> int:
     return lib().oracle_threads()
+
+
+def use_all_cores() -> int:
+    """Give the OpenMP runtime every host core this process may run on (launchers such as torchrun set OMP_NUM_THREADS=1)."""
+    import os
+
+    n = len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else (os.cpu_count() or 1)
+    lib().oracle_set_threads(n)
+    return threads()
 
 
 def mandelbrot_view(W: int, H: int, maxIter: int, x0=-2.0, x1=1.0, y0=-1.5, y1=1.5) -> np.ndarray:
