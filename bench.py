@@ -34,6 +34,16 @@ import numpy as np
 ROOT = Path(__file__).resolve().parent
 sys.path.insert(0, str(ROOT))
 
+_REAL_STDOUT = None
+
+
+def emit(obj):
+    """The one JSON line, on the process's original stdout."""
+    out = _REAL_STDOUT or sys.stdout
+    out.write(json.dumps(obj) + "\n")
+    out.flush()
+
+
 METRIC = "mandelbrot_mpix_per_s"
 UNIT = "Mpix/s"
 W = H = 16384
@@ -159,7 +169,7 @@ def run_reference(args):
         "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
-    print(json.dumps(line))
+    emit(line)
 
 
 # ------------------------------------------------------------------------------------------------ GPU arm helpers
@@ -441,7 +451,7 @@ def run_ours(args):
                          "final_shares": [round(x / items, 4) for x in shares[-1]] if shares else None},
             "workloads": workloads,
         }
-        print(json.dumps(line))
+        emit(line)
     if spmd_mode:
         dist.barrier()
         dist.destroy_process_group()
@@ -474,6 +484,11 @@ def main():
                     help="profiling aid: run just this secondary workload on one GPU and print its numbers")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
+    # stdout carries exactly ONE JSON line: libraries that print banners there (NCCL's version line) go to stderr
+    global _REAL_STDOUT
+    sys.stdout.flush()
+    _REAL_STDOUT = os.fdopen(os.dup(1), "w")
+    os.dup2(2, 1)
     if args.only:
         import cekirdekler_b200 as ck
         from cekirdekler_b200 import kernels
@@ -486,7 +501,7 @@ def main():
             out = bench_nbody(ck, kernels, po, dev, pk, host().ckh_gpu_compute_units(0), args.steps, args.warmup)
         else:
             out = bench_saxpy(ck, kernels, dev, shim(), pk, args.steps, args.warmup)
-        print(json.dumps({"workload": args.only, **out}))
+        emit({"workload": args.only, **out})
     elif args.impl == "reference":
         run_reference(args)
     else:

@@ -80,6 +80,7 @@ def shim() -> C.CDLL:
             "ckEventSynchronize": (None, [vp]),
             "ckHostRegister": (i32, [vp, u64]), "ckHostUnregister": (i32, [vp]), "ckZeroBuffer": (i32, [vp, vp]),
             "ckBroadcastUpload": (i32, [C.POINTER(vp), C.POINTER(vp), i32, vp]),
+            "ckBroadcastCounts": (None, [C.POINTER(u64), C.POINTER(u64)]),
         }
         for name, (res, args) in sig.items():
             fn = getattr(L, name)

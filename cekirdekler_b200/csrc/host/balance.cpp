@@ -76,11 +76,30 @@ void loadBalance(const std::vector<double>& benchmark, bool smooth, BalanceState
         normalized = avg;
     }
 
+    // Step size toward the target split.  The reference always moves 30 % of the way (HelperFunctions.cs:247).  Adaptive
+    // mode moves further while the devices are far from balance — gain = clamp(2 (max/mean - 1), 0.3, 0.9) — and falls back
+    // to the reference's 0.3 near balance, where larger fixed gains oscillate on non-uniform workloads.
+    double gain = 0.3;
+    if (mode == BalancerMode::Adaptive) {
+        double mx = 0.0, sm = 0.0;
+        int act = 0;
+        for (int i = 0; i < n; i++)
+            if (ranges[i] > 0) {
+                mx = benchmark[i] > mx ? benchmark[i] : mx;
+                sm += benchmark[i];
+                act++;
+            }
+        if (act > 0 && sm > 0.0) {
+            const double g = 2.0 * (mx * act / sm - 1.0);
+            gain = g < 0.3 ? 0.3 : (g > 0.9 ? 0.9 : g);
+        }
+    }
+
     for (int i = 0; i < n; i++) {
         const bool useAverage = smooth && (mode == BalancerMode::Adaptive || st.history[0][0] > 0.00001);
         const double share = useAverage ? normalized[i] : (thr[i] / totalThroughput);
         if (ranges[i] != 0) {
-            tmpRanges[i] = ranges[i] - (int)((ranges[i] - (totalRange * share)) * 0.3);
+            tmpRanges[i] = ranges[i] - (int)((ranges[i] - (totalRange * share)) * gain);
         } else {
             tmpRanges[i] = (int)(((totalRange * (totalBenchmark / (benchmark[i] + 0.01)) / totalThroughput)));
         }

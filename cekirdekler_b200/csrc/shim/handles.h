@@ -199,6 +199,12 @@ bool pinned_lookup(const void* p, int64_t* bytes_out);
 void pinned_add(void* p, int64_t bytes);
 void pinned_remove(void* p);
 
+// NCCL broadcast (ext_nccl.cu); nccl_broadcast returns 0 ok, <0 unavailable, >0 NCCL error
+bool nccl_available();
+int nccl_broadcast(const std::vector<int>& ordinals, const std::vector<void*>& ptrs, const std::vector<cudaStream_t>& streams,
+                   size_t bytes, int root);
+unsigned nccl_next_root(const std::vector<int>& ordinals);
+
 // program front-end (program.cpp)
 std::shared_ptr<Cubin> compile_source(const std::string& user_src, int cc_major, int cc_minor);
 std::string rewrite_kernels(const std::string& src, std::vector<std::pair<std::string, int>>* kernels_out);

@@ -39,6 +39,7 @@ bool cuda_ok(cudaError_t e, const char* what) {
 #define CK_CUDA(call) ck::cuda_ok((call), #call)
 
 static std::atomic<uint64_t> g_launches{0};
+static std::atomic<uint64_t> g_broadcasts_nccl{0}, g_broadcasts_p2p{0};
 
 // ------------------------------------------------------------------ registry
 Registry& Registry::get() {
@@ -1005,6 +1006,11 @@ int32_t ckZeroBuffer(ck_handle hq, ck_handle hb) {
     return CK_CUDA(cudaMemsetAsync(b->dptr, 0, (size_t)b->bytes(), q->stream)) ? 0 : 2;
 }
 
+void ckBroadcastCounts(uint64_t* viaNccl, uint64_t* viaPeerCopies) {
+    if (viaNccl) *viaNccl = g_broadcasts_nccl.load();
+    if (viaPeerCopies) *viaPeerCopies = g_broadcasts_p2p.load();
+}
+
 int32_t ckBroadcastUpload(ck_handle* hQueues, ck_handle* hBuffers, int32_t n, void* hostArray) {
     if (!hQueues || !hBuffers || n <= 0 || !hostArray) {
         set_error("ckBroadcastUpload: bad arguments");
@@ -1017,7 +1023,34 @@ int32_t ckBroadcastUpload(ck_handle* hQueues, ck_handle* hBuffers, int32_t n, vo
             set_error("ckBroadcastUpload: buffers differ in size");
             return 2;
         }
-    // one host-link upload, then a binary tree of NVLink peer copies: have[] = event marking "data present"
+    // Preferred path: one host-link upload into a rotating root, then ncclBroadcast over NVLink (ext_nccl.cu).
+    bool anyZeroCopy = false, distinct = true;
+    std::vector<int> ords;
+    std::vector<void*> ptrs;
+    std::vector<cudaStream_t> streams;
+    for (int i = 0; i < n; i++) {
+        Buffer* b = as<Buffer>(hBuffers[i]);
+        anyZeroCopy = anyZeroCopy || b->zero_copy;
+        for (int o : ords) distinct = distinct && (o != b->ordinal);
+        ords.push_back(b->ordinal);
+        ptrs.push_back(b->dptr);
+        streams.push_back(as<Queue>(hQueues[i])->stream);
+    }
+    if (n > 1 && !anyZeroCopy && distinct && bytes > 0 && nccl_available()) {
+        const int root = (int)nccl_next_root(ords);
+        Queue* qr = as<Queue>(hQueues[root]);
+        cudaSetDevice(qr->ordinal);
+        if (CK_CUDA(cudaMemcpyAsync(ptrs[root], hostArray, (size_t)bytes, cudaMemcpyHostToDevice, qr->stream))) {
+            const int r = nccl_broadcast(ords, ptrs, streams, (size_t)bytes, root);
+            if (r == 0) {
+                g_broadcasts_nccl.fetch_add(1, std::memory_order_relaxed);
+                return 0;
+            }
+            if (r > 0 && getenv("CK_VERBOSE")) fprintf(stderr, "[KutuphaneCL] NCCL broadcast failed (%s); using peer copies\n", t_last_error.c_str());
+        }
+    }
+    g_broadcasts_p2p.fetch_add(1, std::memory_order_relaxed);
+    // Otherwise: one host-link upload, then a binary tree of NVLink peer copies: have[] = event marking "data present"
     std::vector<cudaEvent_t> have(n, nullptr);
     int rc = 0;
     auto mark = [&](int i) {

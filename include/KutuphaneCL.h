@@ -194,11 +194,14 @@ int32_t   ckHostUnregister(void* ptr);
 /* Fill a device buffer's bytes with zero on a queue (used for histogram outputs). */
 int32_t   ckZeroBuffer(ck_handle hCommandQueue, ck_handle hBuffer);
 
-/* Whole-array broadcast of a `read` input that every device needs: uploads the host array
- * once to buffers[0] over the host link, then fans it out to the other buffers device-to-device over NVLink
- * (binary tree of peer copies; each copy ordered on the receiving device's queue).  All buffers must have
- * the same byte size.  queues[i] is a queue on buffers[i]'s device.  Returns 0 on success. */
+/* Whole-array broadcast of a `read` input that every device needs: uploads the host array once
+ * over the host link into one buffer (the root rotates between calls), then ncclBroadcast carries it to the other
+ * buffers over NVLink, each device's part ordered on its own queue.  When NCCL cannot be loaded (or CK_BROADCAST=p2p)
+ * a binary tree of peer copies from buffers[0] does the same job.  All buffers must have the same byte size and live on
+ * distinct devices; queues[i] is a queue on buffers[i]'s device.  Returns 0 on success. */
 int32_t   ckBroadcastUpload(ck_handle* hQueues, ck_handle* hBuffers, int32_t nDevices, void* hostArray);
+/* How many broadcasts went through NCCL and through peer-copy trees since the library was loaded. */
+void      ckBroadcastCounts(uint64_t* viaNccl, uint64_t* viaPeerCopies);
 
 #ifdef __cplusplus
 }
