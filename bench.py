@@ -385,7 +385,7 @@ def run_ours(args):
     for i in range(args.warmup + args.steps):
         barrier()
         t0 = time.perf_counter()
-        assert g.compute(cr, CID_E2E, "mandelbrot", items, 256, 0, True, ck.PIPELINE_DRIVER, args.e2e_blobs) == 0
+        assert g.compute(cr, CID_E2E, "mandelbrot", items, 256, 0, True, args.e2e_mode == "event", args.e2e_blobs) == 0
         dt = allmax(time.perf_counter() - t0)
         if i >= args.warmup:
             e2e_t.append(dt)
@@ -441,7 +441,7 @@ def run_ours(args):
             "wall_ms_per_step": wall / args.steps * 1e3,
             "clocks": clk,
             "e2e": {"value": e2e_value, "unit": UNIT, "ms_per_step": e2e_ms, "h2d_bytes_per_step": 32 * n_gpus,
-                    "d2h_bytes_per_step": 4 * npix, "mode": f"driver-controlled pipeline, {args.e2e_blobs} blobs, pinned host arrays"},
+                    "d2h_bytes_per_step": 4 * npix, "mode": f"{args.e2e_mode}-controlled pipeline, {args.e2e_blobs} blobs, pinned host arrays"},
             "gpu_launches": launches,
             "roofline": roof,
             "cpu_baseline": line_cpu,
@@ -480,6 +480,7 @@ def main():
     ap.add_argument("--balancer", default="adaptive", choices=["adaptive", "reference"])
     ap.add_argument("--no-all", dest="all", action="store_false", help="skip the SAXPY and n-body workloads")
     ap.add_argument("--e2e-blobs", type=int, default=64, help="pipeline blobs of the end-to-end leg (multiple of 4)")
+    ap.add_argument("--e2e-mode", default="event", choices=["event", "driver"], help="pipelining mode of the end-to-end leg")
     ap.add_argument("--only", default=None, choices=["nbody", "saxpy"],
                     help="profiling aid: run just this secondary workload on one GPU and print its numbers")
     args = ap.parse_args()

@@ -17,8 +17,8 @@
 // two distinct registers.  That matters on Blackwell: an instruction that needs two source registers from the same
 // (even/odd) register bank issues over two cycles, and the textbook y' = fma(x+x, y, cy) — three distinct registers —
 // always does.  Measured on B200 with all lanes in the set (build/exp micro-benchmark, round 1): textbook 5-op form
-// 6.35 issue slots per iteration (63 % of the FP32 peak in 8-FLOP units), this form 4.29 slots (93 %) at MANDEL_K = 32.
-// The escape test is hoisted out of the inner loop: MANDEL_K iterations run unchecked, then one test; if the orbit left
+// 6.35 issue slots per iteration (63 % of the FP32 peak in 8-FLOP units), this form 4.29 slots (93 %) with blocks of 32.
+// The escape test is hoisted out of the inner loop: a block of iterations runs unchecked, then one test; if the orbit left
 // the radius-2 disc inside the block, the block is replayed from its saved start with a per-iteration test to find the
 // exact count.  That is exact because for |c|^2 <= 3.9 an orbit that has left the disc keeps growing
 // (|z'| >= |z|^2 - |c| >= 1.05 |z| once |z| > 2 - 3e-7, far above float rounding error) until it overflows to inf/NaN,
@@ -27,7 +27,11 @@
 // (SURVEY.md §8d), so the issue ceiling of this formulation is 8 / (2 * (4 + overhead)) of the FFMA peak.
 
 #define MANDEL_E 4
-#define MANDEL_K 32
+#define MANDEL_K1 8    // short unchecked blocks first: most pixels outside the set leave within a few iterations, and a
+#define MANDEL_B1 4    // short block keeps both the wasted unchecked work and the replay small for them ...
+#define MANDEL_K2 64   // ... then long blocks, where the per-block test/bookkeeping is 12 instructions per 256 useful ones
+// Measured on the full 16384^2 x 4096 image on B200 (build/exp/mv.cu, round 1): one block length of 32 -> 25.31 ms (78.8 % of
+// the FP32 peak), 64 -> 25.03 ms, 4 blocks of 8 then blocks of 64 -> 24.04 ms (83.0 %); identical iteration counts.
 
 // exact per-iteration loop: at most `limit` iterations from state (x, y); returns the number executed before escape
 __device__ __forceinline__ int mandel_exact(float& x, float& y, const float cx, const float cy, const int limit)
@@ -46,31 +50,44 @@ __device__ __forceinline__ int mandel_exact(float& x, float& y, const float cx, 
     return k;
 }
 
+// One unchecked block of K iterations followed by one escape test.  Returns true when the orbit left the disc somewhere in
+// (n, n + K]; (x, y) is then restored to the block's start so the caller can replay it with the exact test (the test at the
+// block's last state is included, so the replay may run all K iterations: escape exactly at n + K).
+template <int K>
+__device__ __forceinline__ bool mandel_block(float& x, float& y, const float cx, const float cy)
+{
+    const float xs = x, ys = y;
+#pragma unroll
+    for (int u = 0; u < K; u++) {
+        const float t = __fmaf_rn(-y, y, cx);
+        const float w = __fmul_rn(x, y);
+        y = __fmaf_rn(2.0f, w, cy);
+        x = __fmaf_rn(x, x, t);
+    }
+    const float m = __fmaf_rn(x, x, __fmul_rn(y, y));
+    if (!(m <= 4.0f)) {
+        x = xs;
+        y = ys;
+        return true;
+    }
+    return false;
+}
+
 __device__ __forceinline__ int mandel_pixel(const float cx, const float cy, const int maxIter)
 {
     float x = 0.0f, y = 0.0f;
     int n = 0;
     const float c2 = __fmaf_rn(cx, cx, __fmul_rn(cy, cy));
     if (c2 <= 3.9f) {
-        // blocks of MANDEL_K unchecked iterations
-        while (n + MANDEL_K <= maxIter) {
-            const float xs = x, ys = y;
-#pragma unroll
-            for (int u = 0; u < MANDEL_K; u++) {
-                const float t = __fmaf_rn(-y, y, cx);
-                const float w = __fmul_rn(x, y);
-                y = __fmaf_rn(2.0f, w, cy);
-                x = __fmaf_rn(x, x, t);
-            }
-            const float m = __fmaf_rn(x, x, __fmul_rn(y, y));
-            if (!(m <= 4.0f)) {
-                // left the disc somewhere in (n, n + K]: replay this block with the exact test.  The test at the
-                // block's last state is included, so the replay may run all K iterations (escape exactly at n + K).
-                x = xs;
-                y = ys;
-                return n + mandel_exact(x, y, cx, cy, MANDEL_K);
-            }
-            n += MANDEL_K;
+#pragma unroll 1
+        for (int b = 0; b < MANDEL_B1 && n + MANDEL_K1 <= maxIter; b++) {
+            if (mandel_block<MANDEL_K1>(x, y, cx, cy)) return n + mandel_exact(x, y, cx, cy, MANDEL_K1);
+            n += MANDEL_K1;
+        }
+#pragma unroll 1
+        for (int blocks = (maxIter - n) / MANDEL_K2; blocks > 0; blocks--) {
+            if (mandel_block<MANDEL_K2>(x, y, cx, cy)) return n + mandel_exact(x, y, cx, cy, MANDEL_K2);
+            n += MANDEL_K2;
         }
     }
     return n + mandel_exact(x, y, cx, cy, maxIter - n);

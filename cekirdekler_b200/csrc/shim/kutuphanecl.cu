@@ -769,7 +769,9 @@ ck_handle createBuffer(ck_handle hContext, int32_t numberOfElements, int32_t clA
             return nullptr;
         }
         // device-resident arrays (no read/write flag) are never uploaded: start them at zero like the host arrays they mirror
-        CK_CUDA(cudaMemset(b->dptr, 0, bytes));
+        // (completed before the handle is returned: the queues are non-blocking streams, so a clear still pending on the
+        // default stream would otherwise be free to land after the first kernel has written the buffer)
+        if (CK_CUDA(cudaMemsetAsync(b->dptr, 0, bytes, cudaStreamPerThread))) CK_CUDA(cudaStreamSynchronize(cudaStreamPerThread));
     }
     b->ctx = c;
     c->retain();

@@ -58,9 +58,9 @@ def test_mandelbrot_c1_bit_exact_against_oracle_and_golden(gpus):
 
 
 @pytest.mark.parametrize("kernel", ["mandelbrot", "mandelbrot1"])
-@pytest.mark.parametrize("max_iter", [1, 31, 32, 33, 64, 100, 1000])
+@pytest.mark.parametrize("max_iter", [1, 7, 8, 9, 31, 32, 33, 95, 96, 97, 100, 1000])
 def test_mandelbrot_iteration_limits(gpus, kernel, max_iter):
-    # max_iter around the unchecked-block length (32) exercises the block/tail/replay boundaries
+    # max_iter around the unchecked-block boundaries (4 blocks of 8, then blocks of 64) exercises the block/tail/replay boundaries
     got, _ = run_mandelbrot(gpu0(), 512, 256, max_iter, kernel)
     exp = po.mandelbrot(po.mandelbrot_view(512, 256, max_iter), 512 * 256)
     assert np.array_equal(got, exp)
