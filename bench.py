@@ -479,7 +479,7 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--balancer", default="adaptive", choices=["adaptive", "reference"])
     ap.add_argument("--no-all", dest="all", action="store_false", help="skip the SAXPY and n-body workloads")
-    ap.add_argument("--e2e-blobs", type=int, default=64, help="pipeline blobs of the end-to-end leg (multiple of 4)")
+    ap.add_argument("--e2e-blobs", type=int, default=16, help="pipeline blobs of the end-to-end leg (multiple of 4)")
     ap.add_argument("--e2e-mode", default="event", choices=["event", "driver"], help="pipelining mode of the end-to-end leg")
     ap.add_argument("--only", default=None, choices=["nbody", "saxpy"],
                     help="profiling aid: run just this secondary workload on one GPU and print its numbers")
