@@ -8,6 +8,7 @@ void BalanceState::reset(int devices) {
     history.assign(kHistoryDepth, std::vector<double>(devices, 0.0));
     lastThroughputs.assign(devices, 0.0);
     valid = 0;
+    lastImbalance = 0.0;
 }
 
 static int maxIndex(const std::vector<int>& a) {  // first index holding the maximum (HelperFunctions.cs:84-97)
@@ -77,8 +78,9 @@ void loadBalance(const std::vector<double>& benchmark, bool smooth, BalanceState
     }
 
     // Step size toward the target split.  The reference always moves 30 % of the way (HelperFunctions.cs:247).  Adaptive
-    // mode moves further while the devices are far from balance — gain = clamp(2 (max/mean - 1), 0.3, 0.9) — and falls back
-    // to the reference's 0.3 near balance, where larger fixed gains oscillate on non-uniform workloads.
+    // mode moves further while the devices are far from balance — gain = clamp(2 (max/mean - 1), 0.3, 0.6) — and uses the
+    // reference's 0.3 near balance and whenever the imbalance grew since the previous call.  (Larger gains oscillate on
+    // non-uniform workloads: with timing noise a 0.9 cap diverged on 8 GPUs in round 1, in the simulation and on the box.)
     double gain = 0.3;
     if (mode == BalancerMode::Adaptive) {
         double mx = 0.0, sm = 0.0;
@@ -90,8 +92,11 @@ void loadBalance(const std::vector<double>& benchmark, bool smooth, BalanceState
                 act++;
             }
         if (act > 0 && sm > 0.0) {
-            const double g = 2.0 * (mx * act / sm - 1.0);
-            gain = g < 0.3 ? 0.3 : (g > 0.9 ? 0.9 : g);
+            const double imbalance = mx * act / sm;
+            const double g = 2.0 * (imbalance - 1.0);
+            gain = g < 0.3 ? 0.3 : (g > 0.6 ? 0.6 : g);
+            if (st.lastImbalance > 0.0 && imbalance > 1.02 * st.lastImbalance) gain = 0.3;
+            st.lastImbalance = imbalance;
         }
     }
 

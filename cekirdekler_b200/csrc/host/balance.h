@@ -23,6 +23,7 @@ struct BalanceState {
     // normalised throughput shares, oldest first: history[k][device]
     std::vector<std::vector<double>> history;
     std::vector<double> lastThroughputs;  // Cores.tmpThroughputs — exposed as normalizedComputePowersOfDevices
+    double lastImbalance = 0.0;  // Adaptive mode: max/mean device time seen by the previous call
     int valid = 0;  // Adaptive mode: newest history rows that belong to the current balanced regime
     void reset(int devices);
 };

@@ -394,6 +394,9 @@ void Cores::compute(const std::vector<std::string>& kernelNames, int numRepeats,
         } else {
             forEachWorker([&](int i) { phase1(i); phase23(i); }, threaded);
         }
+        if (!threaded)
+            for (int i = 0; i < W; i++)
+                if (ranges[i] > 0) workers_[i]->stopBench();  // every device's stop event goes in before the first wait
         forEachWorker(drain, threaded);
     }
     lastUsedComputeId = computeId;

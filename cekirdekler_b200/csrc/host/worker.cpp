@@ -328,12 +328,23 @@ void Worker::startBench(bool deviceClock) {
     timerRunning_ = true;
 }
 
+void Worker::stopBench() {
+    // Records the end of the device span now, without waiting for it.  When one host thread drives several devices it must
+    // do this for ALL of them before it blocks on any: an event's time stamp cannot be earlier than the moment it was
+    // enqueued, so a stop event recorded after waiting for device 0 would charge device 0's run time to device 1.
+    if (timerRunning_ && deviceClock_ && !stopRecorded_) {
+        ckTimerStop(timer_, q_[0]);
+        stopRecorded_ = true;
+    }
+}
+
 void Worker::endBench(int computeId) {
     if (!timerRunning_) return;
     timerRunning_ = false;
     double ms;
     if (deviceClock_) {
-        ckTimerStop(timer_, q_[0]);
+        if (!stopRecorded_) ckTimerStop(timer_, q_[0]);
+        stopRecorded_ = false;
         ms = ckTimerElapsedMs(timer_);
         if (ms < 0) ms = 0;
     } else {

@@ -102,6 +102,7 @@ class Worker {
     // ---- balancer clock (Worker.cs:753-807) ----
     void benchmark0(int computeId) { bench_[computeId] = 0.0; }
     void startBench(bool deviceClock);
+    void stopBench();
     void endBench(int computeId);
     double benchmark(int computeId) const;
 
@@ -142,6 +143,7 @@ class Worker {
     ck_handle timer_ = nullptr;
     bool timerRunning_ = false;
     bool deviceClock_ = false;
+    bool stopRecorded_ = false;
     std::chrono::steady_clock::time_point t0_;
 };
 

@@ -73,8 +73,9 @@ def test_copy_matrix(gpus, kind, tname, multi, pipe, kernel_list, flags):
         rc = g.compute(cr, cid, kernel_list, N, 256)
     else:
         rc = g.compute(cr, cid, kernel_list, N, 64, 0, True, pipe == "event", 4)
-    if multi and pipe != "none" and cr.numberOfDevices * 64 * 4 > N:
-        assert rc != 0  # the reference refuses: global range < devices*local*blobs (ClArray.cs:1649-1657)
+    needed = cr.numberOfDevices * (256 if pipe == "none" else 64 * 4)
+    if multi and needed > N:
+        assert rc != 0  # the reference refuses: global range < devices*local(*blobs) (ClArray.cs:1640-1657)
         cr_err = cr.numberOfErrorsHappened
         assert cr_err >= 1
         _crunchers.pop((tname, multi))  # a cruncher that has errored stays inert, as in the reference
