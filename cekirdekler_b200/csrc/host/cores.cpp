@@ -331,8 +331,12 @@ void Cores::compute(const std::vector<std::string>& kernelNames, int numRepeats,
             if (!enq) w.startBench(deviceClock);
             w.writeToBuffer(arrs, refs[0], ranges[0], /*enqueueMode=*/true, cq);  // in-order queue: no host sync needed before the kernel
             launchKernels(0);
-            w.readFromBuffer(arrs, refs[0], ranges[0], base, D, enq, cq);
-            if (!enq) w.endBench(computeId);
+            w.readFromBuffer(arrs, refs[0], ranges[0], base, D, /*enqueueMode=*/true, cq);
+            if (!enq) {
+                w.stopBench();  // the span ends when the download does, not when the host thread wakes up from the wait
+                finish(w.mainQueue());
+                w.endBench(computeId);
+            }
             if (enq) {
                 w.markQueueUsed(w.mainQueue());
                 if (fineGrainedQueueControl && enqueueModeAsync_) w.addMarker(w.lastUsedQueue() ? w.lastUsedQueue() : w.mainQueue());

@@ -12,7 +12,7 @@
 //             pos is a whole-array `read` input (every device needs all of it: the one broadcast of the path).  The
 //             inverse square root is the raw SFU approximation (MUFU.RSQ); parity with the oracle is <= 1e-4 relative
 //             on positions.  One work-item = one body (numberOfElementsPerWorkItem = 4 floats on vel/posOut); the
-//             work-group size must be a multiple of 64 and at least 128.  The j loop runs over PAIRS of bodies with
+//             work-group size must be a multiple of 128.  The j loop runs over PAIRS of bodies with
 //             Blackwell's packed two-lane FP32 instructions (FADD2/FMUL2/FFMA2, PTX *.f32x2): each issue slot carries
 //             two interactions.  Measured on B200 (build/exp micro-benchmark, round 1, per-SM cycles per
 //             warp-interaction): scalar 1 body/thread 17.9, packed pairs with 2 bodies/thread 15.9; the floor is 12
@@ -122,54 +122,63 @@ __device__ __forceinline__ ck_f32x2 ck_sub2(ck_f32x2 a, ck_f32x2 b) { ck_f32x2 d
         AZ = ck_fma2(DZ, S, AZ);                                                             \
     }
 
-// Work decomposition inside a work-group of L work-items (L a multiple of 64; one work-item = one body, so the group owns
-// L consecutive bodies): the group is split in two halves of L/2 threads.  Thread q of either half carries the PAIR of
-// bodies (2q, 2q+1) of the group; half 0 sweeps the first half of the j tiles, half 1 the second half, and the partial
-// accelerations are combined through shared memory at the end.  Each thread therefore gets the two-bodies-per-thread
-// operand reuse (one pair of LDS.128 feeds 4 interactions) while the grid still has one thread per body — 131072 bodies
-// give 4096 warps, 6.9 per SM sub-partition, instead of 3.5 (which would both starve the schedulers and leave 13 % of
-// the SMs' time to warp-count rounding).  The next tile is prefetched into registers while the current one is consumed.
-#define NB_PREFETCH 4   // float4 loads per thread per tile: NB_TILE / (L/2) must not exceed this (L >= 128)
+// Work decomposition of nBody3D inside a work-group of L work-items (L a multiple of 128; one work-item = one body, so the
+// group owns L consecutive bodies): the group is cut into NB_B = 4 slices of L/4 threads.  Thread q of every slice carries
+// the same FOUR bodies (4q .. 4q+3 of the group); slice s sweeps the s-th quarter of the j tiles, and the partial
+// accelerations are combined through shared memory at the end.  Each thread thus reuses one pair of LDS.128 for 8
+// interactions and keeps 4 independent dependency chains in flight, while the grid still has one thread per body.
+// Measured on B200 (build/exp/nb2.cu, round 1, 131072 bodies): 2 bodies per thread 8.29 ms, 4 bodies per thread 7.61 ms.
+// The next tile is prefetched into registers while the current one is consumed.
+#define NB_B 4          // bodies per thread = j slices per work-group
+#define NB_PREFETCH 8   // float4 loads per thread per tile: NB_TILE / (L / NB_B) must not exceed this (L >= 128)
 
 __kernel void nBody3D(const float4* __restrict__ pos, float4* __restrict__ vel, float4* __restrict__ posOut,
                       const float* __restrict__ params)
 {
-    // per half: a tile of NB_TILE bodies stored as NB_TILE/2 pairs, sA[p] = (x0, x1, y0, y1), sB[p] = (z0, z1, m0, m1),
+    // per slice: a tile of NB_TILE bodies stored as NB_TILE/2 pairs, sA[p] = (x0, x1, y0, y1), sB[p] = (z0, z1, m0, m1),
     // so one broadcast LDS.128 delivers two aligned register pairs = two packed operands
-    __shared__ float4 sA[2][NB_TILE / 2];
-    __shared__ float4 sB[2][NB_TILE / 2];
-    __shared__ float red[6][NB_TILE];       // half 1's partial accelerations (6 per thread, up to 256 threads per half)
+    __shared__ float4 sA[NB_B][NB_TILE / 2];
+    __shared__ float4 sB[NB_B][NB_TILE / 2];
+    __shared__ float red[3 * NB_B][NB_TILE];   // partial accelerations of slices 1..3 (3 per body, up to 256 threads per slice)
     const float dt = __ldg(params + 0), eps2 = __ldg(params + 1);
     const int n = (int)__ldg(params + 2);
-    const int L2 = blockDim.x >> 1;                              // threads per half
-    const int half = (threadIdx.x >= L2) ? 1 : 0;
-    const int q = threadIdx.x - half * L2;                       // pair index inside the group
+    const int LS = blockDim.x / NB_B;                            // threads per slice
+    const int slice = threadIdx.x / LS;
+    const int q = threadIdx.x - slice * LS;
     const int groupFirst = (int)get_global_id(0) - threadIdx.x;  // first body of this work-group
-    const int i0 = groupFirst + 2 * q, i1 = i0 + 1;
-    const float4 p0 = pos[i0], p1 = pos[i1];
-    const ck_f32x2 P0X = ck_pack(p0.x, p0.x), P0Y = ck_pack(p0.y, p0.y), P0Z = ck_pack(p0.z, p0.z);
-    const ck_f32x2 P1X = ck_pack(p1.x, p1.x), P1Y = ck_pack(p1.y, p1.y), P1Z = ck_pack(p1.z, p1.z);
+    const int i0 = groupFirst + NB_B * q;
+    float4 pb[NB_B];
+    ck_f32x2 PIX[NB_B], PIY[NB_B], PIZ[NB_B], AX[NB_B], AY[NB_B], AZ[NB_B];
+#pragma unroll
+    for (int b = 0; b < NB_B; b++) {
+        pb[b] = pos[i0 + b];
+        PIX[b] = ck_pack(pb[b].x, pb[b].x);
+        PIY[b] = ck_pack(pb[b].y, pb[b].y);
+        PIZ[b] = ck_pack(pb[b].z, pb[b].z);
+        AX[b] = ck_pack(0.0f, 0.0f);
+        AY[b] = AX[b];
+        AZ[b] = AX[b];
+    }
     const ck_f32x2 EPS = ck_pack(eps2, eps2);
-    ck_f32x2 AX = ck_pack(0.0f, 0.0f), AY = AX, AZ = AX, BX = AX, BY = AX, BZ = AX;
 
     const int tiles = (n + NB_TILE - 1) / NB_TILE;
-    const int tilesPerHalf = (tiles + 1) >> 1;                   // both halves run the same trip count (barriers must match)
-    const int firstTile = half * tilesPerHalf;
-    float* fA = reinterpret_cast<float*>(sA[half]);
-    float* fB = reinterpret_cast<float*>(sB[half]);
+    const int tilesPerSlice = (tiles + NB_B - 1) / NB_B;         // every slice runs the same trip count (barriers must match)
+    const int firstTile = slice * tilesPerSlice;
+    float* fA = reinterpret_cast<float*>(sA[slice]);
+    float* fB = reinterpret_cast<float*>(sB[slice]);
 
     float4 nxt[NB_PREFETCH];
 #pragma unroll
     for (int k = 0; k < NB_PREFETCH; k++) {
-        const int t = q + k * L2;
+        const int t = q + k * LS;
         const int j = firstTile * NB_TILE + t;
-        nxt[k] = (t < NB_TILE && j < n && firstTile < tiles) ? pos[j] : make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+        nxt[k] = (t < NB_TILE && firstTile < tiles && j < n) ? pos[j] : make_float4(0.0f, 0.0f, 0.0f, 0.0f);
     }
-    for (int it = 0; it < tilesPerHalf; it++) {
+    for (int it = 0; it < tilesPerSlice; it++) {
         // stage the prefetched tile (padding bodies have mass 0 and contribute nothing)
 #pragma unroll
         for (int k = 0; k < NB_PREFETCH; k++) {
-            const int t = q + k * L2;
+            const int t = q + k * LS;
             if (t < NB_TILE) {
                 const int p = t >> 1, h = t & 1;
                 fA[p * 4 + h] = nxt[k].x;
@@ -183,48 +192,114 @@ __kernel void nBody3D(const float4* __restrict__ pos, float4* __restrict__ vel, 
         const int nextTile = firstTile + it + 1;
 #pragma unroll
         for (int k = 0; k < NB_PREFETCH; k++) {
-            const int t = q + k * L2;
+            const int t = q + k * LS;
             const int j = nextTile * NB_TILE + t;
-            const bool live = (it + 1 < tilesPerHalf) && (nextTile < tiles) && (t < NB_TILE) && (j < n);
+            const bool live = (it + 1 < tilesPerSlice) && (nextTile < tiles) && (t < NB_TILE) && (j < n);
             nxt[k] = live ? pos[j] : make_float4(0.0f, 0.0f, 0.0f, 0.0f);
         }
-        const float4* tA = sA[half];
-        const float4* tB = sB[half];
+        const float4* tA = sA[slice];
+        const float4* tB = sB[slice];
 #pragma unroll 2
         for (int t = 0; t < NB_TILE / 2; t++) {
-            const float4 a = tA[t], b = tB[t];
-            const ck_f32x2 PX = ck_pack(a.x, a.y), PY = ck_pack(a.z, a.w), PZ = ck_pack(b.x, b.y), PM = ck_pack(b.z, b.w);
-            NB_PAIR_INTERACT(P0X, P0Y, P0Z, AX, AY, AZ)
-            NB_PAIR_INTERACT(P1X, P1Y, P1Z, BX, BY, BZ)
+            const float4 a = tA[t], b4 = tB[t];
+            const ck_f32x2 PX = ck_pack(a.x, a.y), PY = ck_pack(a.z, a.w), PZ = ck_pack(b4.x, b4.y), PM = ck_pack(b4.z, b4.w);
+#pragma unroll
+            for (int b = 0; b < NB_B; b++) NB_PAIR_INTERACT(PIX[b], PIY[b], PIZ[b], AX[b], AY[b], AZ[b])
         }
         __syncthreads();
     }
-    float a0x, a0y, a0z, a1x, a1y, a1z, lo, hi;
-    ck_unpack(AX, lo, hi); a0x = lo + hi;
-    ck_unpack(AY, lo, hi); a0y = lo + hi;
-    ck_unpack(AZ, lo, hi); a0z = lo + hi;
-    ck_unpack(BX, lo, hi); a1x = lo + hi;
-    ck_unpack(BY, lo, hi); a1y = lo + hi;
-    ck_unpack(BZ, lo, hi); a1z = lo + hi;
-    if (half == 1) {
-        red[0][q] = a0x; red[1][q] = a0y; red[2][q] = a0z;
-        red[3][q] = a1x; red[4][q] = a1y; red[5][q] = a1z;
+    float ax[NB_B], ay[NB_B], az[NB_B];
+#pragma unroll
+    for (int b = 0; b < NB_B; b++) {
+        float lo, hi;
+        ck_unpack(AX[b], lo, hi); ax[b] = lo + hi;
+        ck_unpack(AY[b], lo, hi); ay[b] = lo + hi;
+        ck_unpack(AZ[b], lo, hi); az[b] = lo + hi;
     }
-    __syncthreads();
-    if (half == 0) {
-        a0x += red[0][q]; a0y += red[1][q]; a0z += red[2][q];
-        a1x += red[3][q]; a1y += red[4][q]; a1z += red[5][q];
-        float4 v = vel[i0];
-        v.x = __fmaf_rn(a0x, dt, v.x);
-        v.y = __fmaf_rn(a0y, dt, v.y);
-        v.z = __fmaf_rn(a0z, dt, v.z);
-        vel[i0] = v;
-        posOut[i0] = make_float4(__fmaf_rn(v.x, dt, p0.x), __fmaf_rn(v.y, dt, p0.y), __fmaf_rn(v.z, dt, p0.z), p0.w);
-        v = vel[i1];
-        v.x = __fmaf_rn(a1x, dt, v.x);
-        v.y = __fmaf_rn(a1y, dt, v.y);
-        v.z = __fmaf_rn(a1z, dt, v.z);
-        vel[i1] = v;
-        posOut[i1] = make_float4(__fmaf_rn(v.x, dt, p1.x), __fmaf_rn(v.y, dt, p1.y), __fmaf_rn(v.z, dt, p1.z), p1.w);
+    // slices 1..3 hand their partial sums to slice 0, one after the other (fixed order: results do not depend on timing)
+    for (int s = 1; s < NB_B; s++) {
+        if (slice == s) {
+#pragma unroll
+            for (int b = 0; b < NB_B; b++) {
+                red[3 * b][q] = ax[b];
+                red[3 * b + 1][q] = ay[b];
+                red[3 * b + 2][q] = az[b];
+            }
+        }
+        __syncthreads();
+        if (slice == 0) {
+#pragma unroll
+            for (int b = 0; b < NB_B; b++) {
+                ax[b] += red[3 * b][q];
+                ay[b] += red[3 * b + 1][q];
+                az[b] += red[3 * b + 2][q];
+            }
+        }
+        __syncthreads();
+    }
+    if (slice == 0) {
+#pragma unroll
+        for (int b = 0; b < NB_B; b++) {
+            float4 v = vel[i0 + b];
+            v.x = __fmaf_rn(ax[b], dt, v.x);
+            v.y = __fmaf_rn(ay[b], dt, v.y);
+            v.z = __fmaf_rn(az[b], dt, v.z);
+            vel[i0 + b] = v;
+            posOut[i0 + b] = make_float4(__fmaf_rn(v.x, dt, pb[b].x), __fmaf_rn(v.y, dt, pb[b].y), __fmaf_rn(v.z, dt, pb[b].z), pb[b].w);
+        }
+    }
+}
+
+// nBody3Dq — the same step with FOUR work-items per body (global range = 4 n, numberOfElementsPerWorkItem = 1 float on
+// vel/posOut, so work-item w still owns float w of those arrays and every device's share is a whole number of bodies).
+// The four adjacent lanes of a body each sweep a quarter of every tile (pairs 4m + lane) and combine with two shuffles.
+// It trades operand reuse for parallelism: meant for small per-device shares (an 8-way split of 131072 bodies leaves a
+// device 512 warps with nBody3D — fewer than its 592 schedulers — but 2048 with this kernel).
+__kernel void nBody3Dq(const float4* __restrict__ pos, float4* __restrict__ vel, float4* __restrict__ posOut,
+                       const float* __restrict__ params)
+{
+    __shared__ float4 sA[NB_TILE / 2];
+    __shared__ float4 sB[NB_TILE / 2];
+    float* fA = reinterpret_cast<float*>(sA);
+    float* fB = reinterpret_cast<float*>(sB);
+    const float dt = __ldg(params + 0), eps2 = __ldg(params + 1);
+    const int n = (int)__ldg(params + 2);
+    const unsigned int w = (unsigned int)get_global_id(0);
+    const int i = (int)(w >> 2), lane4 = (int)(w & 3u);
+    const float4 pi = pos[i];
+    const ck_f32x2 PIX = ck_pack(pi.x, pi.x), PIY = ck_pack(pi.y, pi.y), PIZ = ck_pack(pi.z, pi.z), EPS = ck_pack(eps2, eps2);
+    ck_f32x2 AX = ck_pack(0.0f, 0.0f), AY = AX, AZ = AX;
+    for (int base = 0; base < n; base += NB_TILE) {
+        for (int t = threadIdx.x; t < NB_TILE; t += blockDim.x) {
+            const int j = base + t;
+            const float4 pj = (j < n) ? pos[j] : make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+            const int p = t >> 1, h = t & 1;
+            fA[p * 4 + h] = pj.x;
+            fA[p * 4 + 2 + h] = pj.y;
+            fB[p * 4 + h] = pj.z;
+            fB[p * 4 + 2 + h] = pj.w;
+        }
+        __syncthreads();
+#pragma unroll 4
+        for (int m = 0; m < NB_TILE / 8; m++) {
+            const float4 a = sA[4 * m + lane4], b4 = sB[4 * m + lane4];   // a warp reads 64 contiguous bytes: one wavefront
+            const ck_f32x2 PX = ck_pack(a.x, a.y), PY = ck_pack(a.z, a.w), PZ = ck_pack(b4.x, b4.y), PM = ck_pack(b4.z, b4.w);
+            NB_PAIR_INTERACT(PIX, PIY, PIZ, AX, AY, AZ)
+        }
+        __syncthreads();
+    }
+    float lo, hi;
+    ck_unpack(AX, lo, hi); float ax = lo + hi;
+    ck_unpack(AY, lo, hi); float ay = lo + hi;
+    ck_unpack(AZ, lo, hi); float az = lo + hi;
+    ax += __shfl_xor_sync(0xffffffffu, ax, 1); ay += __shfl_xor_sync(0xffffffffu, ay, 1); az += __shfl_xor_sync(0xffffffffu, az, 1);
+    ax += __shfl_xor_sync(0xffffffffu, ax, 2); ay += __shfl_xor_sync(0xffffffffu, ay, 2); az += __shfl_xor_sync(0xffffffffu, az, 2);
+    if (lane4 == 0) {
+        float4 v = vel[i];
+        v.x = __fmaf_rn(ax, dt, v.x);
+        v.y = __fmaf_rn(ay, dt, v.y);
+        v.z = __fmaf_rn(az, dt, v.z);
+        vel[i] = v;
+        posOut[i] = make_float4(__fmaf_rn(v.x, dt, pi.x), __fmaf_rn(v.y, dt, pi.y), __fmaf_rn(v.z, dt, pi.z), pi.w);
     }
 }

@@ -236,9 +236,9 @@ def nbody3d_inputs(n, seed=0xC0FFEE + 10):
     return pos
 
 
-@pytest.mark.parametrize("kernel,bodies_per_item,local", [("nBody3D", 1, 128), ("nBody3D", 1, 256), ("nBody3D1", 1, 256)])
+@pytest.mark.parametrize("kernel,items_per_body,local", [("nBody3D", 1, 128), ("nBody3D", 1, 256), ("nBody3D1", 1, 256), ("nBody3Dq", 4, 256)])
 @pytest.mark.parametrize("n,steps", [(2048, 1), (16384, 10)])
-def test_nbody3d_positions_within_1e4_relative(gpus, n, steps, kernel, bodies_per_item, local):
+def test_nbody3d_positions_within_1e4_relative(gpus, n, steps, kernel, items_per_body, local):
     pos0 = nbody3d_inputs(n)
     params_h = np.array([1e-3, 1e-4, n, 0], np.float32)
     # oracle
@@ -254,14 +254,14 @@ def test_nbody3d_positions_within_1e4_relative(gpus, n, steps, kernel, bodies_pe
     params.view[:] = params_h
     params.readOnly = True
     vel.partialRead, vel.read = True, False
-    vel.numberOfElementsPerWorkItem = 4 * bodies_per_item
+    vel.numberOfElementsPerWorkItem = 4 // items_per_body
     for arr in (pa, pb):
-        arr.numberOfElementsPerWorkItem = 4 * bodies_per_item
+        arr.numberOfElementsPerWorkItem = 4 // items_per_body
     src, dst = pa, pb
     for _ in range(steps):
         src.read, src.partialRead, src.write = True, False, False      # input: whole array to every device
         dst.read, dst.partialRead, dst.write = False, False, True      # output: each device's slice
-        assert src.nextParam(vel, dst, params).compute(cr, 1, kernel, n // bodies_per_item, local) == 0
+        assert src.nextParam(vel, dst, params).compute(cr, 1, kernel, n * items_per_body, local) == 0
         src, dst = dst, src
     got = src.view.reshape(n, 4)
     exp = p.reshape(n, 4)
