@@ -10,7 +10,7 @@ A "step" is one compute() over the whole image.  Three measurements per run:
   value      Mpix/s with everything resident in HBM (the output stays in the device buffer): CUDA-event time of the
              device span of each compute(), summed over the K steps, max over ranks.
   e2e        the same metric through the public API with HOST buffers: every step uploads the view array and downloads
-             the iteration counts into pinned host memory (driver-controlled pipelining hides the download).
+             the iteration counts into pinned host memory (event-driven pipelining, 16 blobs, hides most of the download).
   roofline   achieved FP32 rate of the Mandelbrot kernel = 8 FLOP x (sum of iteration counts) / kernel time, against
              2 x 128 lanes x SMs x max SM clock (no tensor cores on this path; the bound is the FP32 FMA pipe).
 plus the other BASELINE workloads (streaming SAXPY / vector-add 2^28 floats, n-body 128 Ki bodies) under "workloads",
@@ -116,6 +116,15 @@ class ClockSampler:
         return {"sm_mhz": float(np.median(self.samples)), "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons)}
 
 
+def ncu_traffic(kernel):
+    """DRAM bytes per launch of `kernel` from the committed `ncu --set full` capture (profiles/r1_ncu_summary.json), or None."""
+    f = ROOT / "profiles" / "r1_ncu_summary.json"
+    try:
+        return float(json.loads(f.read_text())[kernel]["traffic_B"])
+    except Exception:
+        return None
+
+
 def dist_env():
     return int(os.environ.get("RANK", "0")), int(os.environ.get("WORLD_SIZE", "1")), int(os.environ.get("LOCAL_RANK", "0"))
 
@@ -178,6 +187,141 @@ def first_stable(imb, tol=1.05, hold=3):
         if all(v <= tol for v in imb[k:k + hold + 1]):
             return k + 1
     return None
+
+
+def bench_hostlink(L, ordinal=0, mib=512, reps=4):
+    """Host-link roofline for the streamed workloads: pinned H2D, D2H and both at once, through the C ABI's own transfers."""
+    import ctypes as C
+
+    n = mib * (1 << 20) // 4
+    lst = L.platformList()
+    plat = L.createPlatform(lst, 0)
+    L.deletePlatformList(lst)
+    dev = L.createDevice(plat, L.CODE_GPU(), ordinal)
+    ctx = L.createContext(plat, dev)
+    q1, q2 = L.createCommandQueue(ctx, dev, 0), L.createCommandQueue(ctx, dev, 0)
+    a1, a2 = L.createArray(n, 4096, 0), L.createArray(n, 4096, 0)
+    h1, h2 = L.alignedArrHead(a1), L.alignedArrHead(a2)
+    b1, b2 = L.createBuffer(ctx, n, 0, 0, h1, 1, 0, 0), L.createBuffer(ctx, n, 0, 0, h2, 1, 0, 0)
+    out = {}
+
+    def timed(fn):
+        fn()
+        L.finish(q1), L.finish(q2)
+        t0 = time.perf_counter()
+        for _ in range(reps):
+            fn()
+        L.finish(q1), L.finish(q2)
+        return (time.perf_counter() - t0) / reps
+
+    byts = n * 4
+    out["h2d_GBps"] = byts / timed(lambda: L.writeToBuffer(q1, b1, h1)) / 1e9
+    out["d2h_GBps"] = byts / timed(lambda: L.readFromBuffer(q2, b2, h2)) / 1e9
+    t = timed(lambda: (L.writeToBuffer(q1, b1, h1), L.readFromBuffer(q2, b2, h2)))
+    out["bidirectional_each_GBps"] = byts / t / 1e9
+    for h, f in ((b1, L.deleteBuffer), (b2, L.deleteBuffer), (a1, L.deleteArray), (a2, L.deleteArray), (q1, L.deleteCommandQueue),
+                 (q2, L.deleteCommandQueue), (ctx, L.deleteContext), (dev, L.deleteDevice), (plat, L.deletePlatform)):
+        f(h)
+    return out
+
+
+def bench_pipeline(ck, kernels, po, n_gpus, frames=24):
+    """C5: blur -> Sobel -> histogram on 3840x2160 float frames, one stage per GPU (all on GPU 0 when fewer), NVLink
+    hand-off vs the reference's host bounce; plus the same frames as independent tasks through the greedy device pool."""
+    from cekirdekler_b200.pipeline import ClPipelineStage
+    from cekirdekler_b200.pool import ClDevicePool, ClDevicePoolType, ClTaskPool, task
+
+    Wf, Hf = 3840, 2160
+    n = Wf * Hf
+    devs = ck.ClPlatforms.all().gpus()
+    d = lambda i: devs[i % max(1, n_gpus)]
+    src = kernels.source("image") + """
+    __kernel void blurStage(const float* in, const int* dims, float* out, int* dimsOut) {
+        const size_t p = get_global_id(0);
+        if (p < 2) dimsOut[p] = dims[p];
+        const int W = dims[0], H = dims[1];
+        if (W <= 0 || H <= 0) return;
+        const int y = (int)(p / (unsigned)W), x = (int)(p - (size_t)y * W);
+        const float c = ck_blur_h(in, W, x, y);
+        const float s1 = __fadd_rn(ck_blur_h(in, W, x, ck_clampi(y - 1, 0, H - 1)), ck_blur_h(in, W, x, ck_clampi(y + 1, 0, H - 1)));
+        const float s2 = __fadd_rn(ck_blur_h(in, W, x, ck_clampi(y - 2, 0, H - 1)), ck_blur_h(in, W, x, ck_clampi(y + 2, 0, H - 1)));
+        out[p] = __fmul_rn(0.00390625f, __fmaf_rn(6.0f, c, __fmaf_rn(4.0f, s1, s2)));
+    }
+    __kernel void sobelStage(const float* in, const int* dims, float* out) {
+        const int W = dims[0], H = dims[1];
+        if (W <= 0 || H <= 0) return;
+        const size_t p = get_global_id(0);
+        const int y = (int)(p / (unsigned)W), x = (int)(p - (size_t)y * W);
+        const int xm = ck_clampi(x - 1, 0, W - 1), xp = ck_clampi(x + 1, 0, W - 1);
+        const int ym = ck_clampi(y - 1, 0, H - 1), yp = ck_clampi(y + 1, 0, H - 1);
+        const float* rm = in + (size_t)ym * W; const float* r0 = in + (size_t)y * W; const float* rp = in + (size_t)yp * W;
+        const float right = __fmaf_rn(2.0f, r0[xp], __fadd_rn(rm[xp], rp[xp]));
+        const float left = __fmaf_rn(2.0f, r0[xm], __fadd_rn(rm[xm], rp[xm]));
+        const float bottom = __fmaf_rn(2.0f, rp[x], __fadd_rn(rp[xm], rp[xp]));
+        const float top = __fmaf_rn(2.0f, rm[x], __fadd_rn(rm[xm], rm[xp]));
+        const float gx = __fsub_rn(right, left), gy = __fsub_rn(bottom, top);
+        out[p] = __fsqrt_rn(__fmaf_rn(gx, gx, __fmul_rn(gy, gy)));
+    }"""
+    frame = ck.ClFloatArray(n)
+    frame.view[:] = po.uniform(0xF00D, n, 0, 1)
+    dims = np.array([Wf, Hf], np.int32)
+    b, s, hexp = np.zeros(n, np.float32), np.zeros(n, np.float32), np.zeros(256, np.uint32)
+    po.blur5x5(frame.view, b, dims)
+    po.sobel(b, s, dims)
+    po.histogram(s, hexp)
+    out = {"frame": f"{Wf}x{Hf} float", "stages_on": [d(i).ordinals[0] for i in range(3)]}
+    for host_fwd in (False, True):
+        blur, sob, hist = ClPipelineStage(), ClPipelineStage(), ClPipelineStage()
+        blur.addDevices(d(0)); blur.addKernels(src, "blurStage", [n], [256])
+        blur.addInputBuffers((np.float32, n), (np.int32, 2)); blur.addOutputBuffers((np.float32, n), (np.int32, 2))
+        sob.addDevices(d(1)); sob.addKernels(src, "sobelStage", [n], [256])
+        sob.addInputBuffers((np.float32, n), (np.int32, 2)); sob.addOutputBuffers((np.float32, n)); sob.appendToStage(blur)
+        hist.addDevices(d(2)); hist.addKernels(src, "histogramZero histogram", [n // 16, n // 16], [256, 256])
+        hist.addInputBuffers((np.float32, n, 16)); hist.addOutputBuffers((np.uint32, 256)); hist.appendToStage(sob)
+        pipe = hist.makePipeline(hostForwarding=host_fwd)
+        assert pipe.errorCode() == 0, pipe.errorMessage()
+        res = np.zeros(256, np.uint32)
+        for _ in range(8):                                   # fill the pipeline (latency 2S+1 pushes)
+            pipe.pushData([frame.view, dims], [res])
+        ok = bool(np.array_equal(res, hexp))
+        t0 = time.perf_counter()
+        for _ in range(frames):
+            pipe.pushData([frame.view, dims], [res])         # mode B: every frame comes from (pinned) host memory
+        dt = (time.perf_counter() - t0) / frames
+        key = "host_bounce" if host_fwd else "nvlink_p2p"
+        out[key] = {"frames_per_s": 1.0 / dt, "ms_per_frame": dt * 1e3, "histogram_exact": ok and bool(np.array_equal(res, hexp))}
+        if not host_fwd:
+            t0 = time.perf_counter()
+            for _ in range(frames):
+                pipe.pushData()                              # mode A: frames already resident on the first device
+            dt = (time.perf_counter() - t0) / frames
+            out["nvlink_p2p_resident"] = {"frames_per_s": 1.0 / dt, "ms_per_frame": dt * 1e3,
+                                          "GBps_algorithmic_hbm": 165.9e6 / dt / 1e9}
+        pipe.dispose()
+    # task pool: independent frames (blur only), greedy over the devices
+    pool = ClDevicePool(ClDevicePoolType.DEVICE_COMPUTE_AT_WILL, kernels.source("image"), True, 3)
+    pool.addDevice(devs[0:max(1, n_gpus)])
+    tp = ClTaskPool()
+    dims_a = ck.ClIntArray(2)
+    dims_a.view[:] = dims
+    dims_a.readOnly = True
+    frame.readOnly = True
+    outs = []
+    ntasks = 32
+    for t in range(ntasks):
+        o = ck.ClFloatArray(n)
+        o.writeOnly = True
+        outs.append(o)
+        tp.feed(task(frame.nextParam(o, dims_a), 1 + t % 3, "gaussianBlur", n, 256))
+    pool.enqueueTaskPool(tp)
+    pool.finish()                                            # warm: buffers and kernels exist now
+    pool.enqueueTaskPool(tp)
+    ms = pool.finish()
+    out["task_pool"] = {"tasks": ntasks, "ms_total": ms, "frames_per_s": ntasks / (ms * 1e-3), "tasks_per_device": pool.tasksPerDevice(),
+                        "exact": bool(np.array_equal(outs[-1].view, b)),
+                        "note": "each task uploads a 33 MB frame and downloads a 33 MB result (host-link bound)"}
+    pool.dispose()
+    return out
 
 
 def bench_saxpy(ck, kernels, dev, shim, pk, steps, warmup):
@@ -268,7 +412,8 @@ def bench_nbody(ck, kernels, po, devs, pk, sms, steps, warmup, spmd_attach=None,
     ach = 20.0 * inter / n_gpus / dt_dev / 1e12   # per-GPU rate: the devices work on their shares concurrently
     res = {"bodies": n, "kernel": kernel, "ms_per_step_device": dt_dev * 1e3, "ms_per_step_e2e": dt_wall * 1e3,
            "GInter_per_s": inter / dt_dev / 1e9, "GInter_per_s_e2e": inter / dt_wall / 1e9,
-           "roofline": {"bound": "fp32", "achieved": ach, "peak": peak, "unit": "TFLOP/s", "frac": ach / peak, "traffic": None,
+           "roofline": {"bound": "fp32", "achieved": ach, "peak": peak, "unit": "TFLOP/s", "frac": ach / peak,
+                        "traffic": ncu_traffic("nbody") if n_gpus == 1 else None,
                         "note": "20 FLOP per interaction; device span includes the 2 MiB position upload and slice transfers"}}
     for a in (pa, pb, vel, params):
         a.dispose()
@@ -427,7 +572,10 @@ def run_ours(args):
     kernel_s = dev_ms / args.steps * 1e-3      # resident leg: the span is the kernel (+ a 32-byte upload)
     ach = flops / n_gpus / kernel_s / 1e12     # per-GPU rate (each GPU runs its share concurrently)
     clk = clocks.summary()
-    roof = {"bound": "fp32", "achieved": ach, "peak": peak_tf, "unit": "TFLOP/s", "frac": ach / peak_tf, "traffic": None,
+    roof = {"bound": "fp32", "achieved": ach, "peak": peak_tf, "unit": "TFLOP/s", "frac": ach / peak_tf,
+            "traffic": ncu_traffic("mandelbrot") if n_gpus == 1 else None,
+            "traffic_note": "DRAM read+write bytes of one launch (ncu --set full, profiles/r1_ncu_summary.json); the algorithmic "
+                            "output is 4 B x 2^28 pixels = 1.074e9 B",
             "kernel": "mandelbrot", "per_gpu": True,
             "algorithmic": f"8 FLOP x {int(total_iters)} executed iterations (sum of the output counts, bit-exact with the oracle)",
             "peak_source": f"2 x 128 lanes x {sms} SMs x {pk['sm_max_mhz']:.0f} MHz ({pk['source']}); no tensor cores on this path",
@@ -435,7 +583,16 @@ def run_ours(args):
 
     workloads = {}
     if args.all and rank == 0 and not spmd_mode:
-        workloads["saxpy_c2"] = bench_saxpy(ck, kernels, devs[0], L, pk, max(2, args.steps // 2), 1)
+        link = bench_hostlink(L, devs.ordinals[0])
+        workloads["host_link"] = link
+        sx = bench_saxpy(ck, kernels, devs[0], L, pk, max(2, args.steps // 2), 1)
+        for mode in ("streamed_event", "streamed_driver"):
+            # streamed roofline: the upload direction carries 8 of the 12 bytes per element and is the binding one
+            sx[mode]["roofline"] = {"bound": "host_link", "achieved": sx[mode]["h2d_GBps"], "peak": link["bidirectional_each_GBps"],
+                                    "unit": "GB/s", "frac": sx[mode]["h2d_GBps"] / link["bidirectional_each_GBps"],
+                                    "peak_source": "pinned H2D with D2H running concurrently, measured in this run"}
+        workloads["saxpy_c2"] = sx
+        workloads["pipeline_c5"] = bench_pipeline(ck, kernels, po, n_gpus)
     if args.all:
         attach = (lambda c: spmd.attach(c, rank, world, torch_dev)) if spmd_mode else None
         nb = bench_nbody(ck, kernels, po, devs, pk, sms, max(3, args.steps), 2, attach, n_gpus, allmax)
@@ -494,7 +651,7 @@ def main():
     ap.add_argument("--no-all", dest="all", action="store_false", help="skip the SAXPY and n-body workloads")
     ap.add_argument("--e2e-blobs", type=int, default=16, help="pipeline blobs of the end-to-end leg (multiple of 4)")
     ap.add_argument("--e2e-mode", default="event", choices=["event", "driver"], help="pipelining mode of the end-to-end leg")
-    ap.add_argument("--only", default=None, choices=["nbody", "saxpy"],
+    ap.add_argument("--only", default=None, choices=["nbody", "saxpy", "pipeline", "hostlink"],
                     help="profiling aid: run just this secondary workload on one GPU and print its numbers")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
@@ -513,6 +670,10 @@ def main():
         pk = peaks()
         if args.only == "nbody":
             out = bench_nbody(ck, kernels, po, dev, pk, host().ckh_gpu_compute_units(0), args.steps, args.warmup)
+        elif args.only == "pipeline":
+            out = bench_pipeline(ck, kernels, po, max(1, args.gpus))
+        elif args.only == "hostlink":
+            out = bench_hostlink(shim())
         else:
             out = bench_saxpy(ck, kernels, dev, shim(), pk, args.steps, args.warmup)
         emit({"workload": args.only, **out})
