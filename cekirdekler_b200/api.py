@@ -94,6 +94,32 @@ class ClDevices:
     def devicesWithDedicatedMemory(self) -> "ClDevices":
         return ClDevices(self.ordinals, self.streamingEnabled)
 
+    def devicesWithHighestDirectNbodyPerformance(self, n: int = 16 * 1024) -> "ClDevices":
+        """Orders the devices by a direct n-body micro-benchmark, fastest first (ClObjectApi.cs:1222-1244 runs
+        Tester.nBody(16K) on each device); here the 2-D reference kernel `nBody2D` at n bodies, timed on the device."""
+        from . import kernels
+
+        x = ClArray(n, np.float32)
+        y = ClArray(n, np.float32)
+        x.view[:] = (np.arange(n) * 0.37) % 30.0 - 15.0
+        y.view[:] = (np.arange(n) * 0.73) % 30.0 - 15.0
+        x.readOnly = True
+        y.readOnly = True
+        nn = ClArray(1, np.int32)
+        nn[0] = n
+        nn.readOnly = True
+        timings = []
+        for o in self.ordinals:
+            cr = ClNumberCruncher(ClDevices([o]), kernels.source("nbody"))
+            fx, fy = ClArray(n, np.float32), ClArray(n, np.float32)
+            fx.writeOnly = True
+            fy.writeOnly = True
+            for _ in range(3):
+                x.nextParam(y, fx, fy, nn).compute(cr, 1, "nBody2D", n, 256)
+            timings.append((cr.benchmarks(1)[0] if cr.errorCode() == 0 else float("inf"), o))
+            cr.dispose()
+        return ClDevices([o for _, o in sorted(timings)], self.streamingEnabled)
+
     def names(self) -> List[str]:
         h = host()
         return [h.ckh_gpu_name(o).decode() for o in self.ordinals]
@@ -262,6 +288,17 @@ class ClArray:
         for a in arrays:
             g._add_any(a, raw_partial_default=False)  # ClArray.cs:1384-1386 (quirk Q11)
         return g
+
+    @staticmethod
+    def wrapArrayOfStructs(structs: np.ndarray) -> "ClArray":
+        """ClArray<byte>.wrapArrayOfStructs (ClArray.cs:1058-1074): a byte view of an array of structs (for example an
+        (n, 3) float32 array standing in for Vector3[]) with numberOfElementsPerWorkItem = the struct's size in bytes."""
+        structs = np.ascontiguousarray(structs)
+        item = structs.dtype.itemsize * int(np.prod(structs.shape[1:], dtype=np.int64)) if structs.ndim > 1 else structs.dtype.itemsize
+        a = ClArray(structs.reshape(-1).view(np.uint8))
+        a.numberOfElementsPerWorkItem = item
+        a._structs = structs
+        return a
 
     def compute(self, cruncher, computeId: int, kernelNamesString: str, globalRange: int, localRange: int = 256,
                 ofsetGlobalRange: int = 0, pipeline: bool = False, pipelineType: bool = PIPELINE_EVENT, pipelineBlobs: int = 4,

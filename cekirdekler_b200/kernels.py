@@ -100,3 +100,21 @@ def reference_nbody_kernel(n: int) -> str:
                     fy[i] = fy0;
                 }
                 """
+
+
+# The Unity sample's kernel, verbatim (/root/reference/Kamera.cs:234-245): Vector3[] arrays arrive as byte arrays wrapped with
+# ClArray<byte>.wrapArrayOfStructs (numberOfElementsPerWorkItem = sizeof(Vector3) = 12) and are read as floats by the kernel.
+REFERENCE_WAVE_EQUATION = """
+                        __kernel void waveEquation( __global float *xyz,__global float *xyzn,__global float *xyzo,__global float * arguments)
+                        {
+                            int threadId=get_global_id(0);
+                            if(threadId<arguments[4])
+                            {
+                                float dx=xyz[threadId*3]-arguments[2];float dy=xyz[threadId*3+1]-arguments[3];float t=arguments[1];
+                                float ctr=arguments[0];float wave=0.02f*ctr*sin(40.0f*t+100.0f*sqrt(dx*dx+dy*dy));
+                                xyzo[threadId*3]=xyz[threadId*3]+xyzn[threadId*3]*wave; // wave equation for all surface vertices
+                                xyzo[threadId*3+1]=xyz[threadId*3+1]+xyzn[threadId*3+1]*wave; // wave equation for all surface vertices
+                                xyzo[threadId*3+2]=xyz[threadId*3+2]+xyzn[threadId*3+2]*wave; // wave equation for all surface vertices
+                            }
+                        }
+                    """

@@ -8,6 +8,7 @@
 //   oracle_copy         the `test` copy kernels                      Tester.cs:35-38 (and the 6 other element types)
 //   oracle_vector_add   `vectorAdd`  c[i]=a[i]+b[i]                  Tester.cs:7820-7824
 //   oracle_nbody2d      the host n-body loop = the `nBody` kernel    Tester.cs:7702-7716 / :7727-7742 (quirk Q3 kept: fy uses dx)
+//   oracle_wave_equation  the CPU branch of the Unity sample         /root/reference/Kamera.cs:213-218
 // Kernels that BASELINE.json names but the reference does not contain have NO reference source and NO
 // reference vectors: their arithmetic is DEFINED here and in cekirdekler_b200/csrc/kernels/*.cu, operation by operation,
 // so both sides can be bit-exact.  PARITY UNPINNED for: oracle_mandelbrot, oracle_saxpy, oracle_nbody3d_step,
@@ -163,6 +164,23 @@ void oracle_nbody3d_step(const float* pos, float* vel, float* posOut, const floa
         posOut[4 * i + 1] = fmaf(vy, dt, yi);
         posOut[4 * i + 2] = fmaf(vz, dt, zi);
         posOut[4 * i + 3] = pos[4 * i + 3];
+    }
+}
+
+// ---------------------------------------------------------------- waveEquation (Kamera.cs:213-218, the reference's own CPU loop)
+// vertices[i] = verticesBase[i] + 0.02f * normals[i] * ctr * (float)sin(40 t + 100 sqrt(dx^2 + dy^2)),  dx/dy measured from (x, y);
+// arguments = { ctr, t, x, y, n } as the kernel receives them (Kamera.cs:257-262).  Vector3 arrays are plain xyz float triples.
+void oracle_wave_equation(const float* xyz, const float* xyzn, float* xyzo, const float* arguments, long long offset, long long count) {
+    const float ctr = arguments[0], t = arguments[1], x = arguments[2], y = arguments[3];
+    const long long n = (long long)arguments[4];
+#pragma omp parallel for schedule(static)
+    for (long long i = offset; i < offset + count; i++) {
+        if (i >= n) continue;
+        const float dx = xyz[3 * i] - x, dy = xyz[3 * i + 1] - y;
+        const float wave = 0.02f * ctr * (float)sin(40.0f * t + 100.0f * sqrt((double)(dx * dx + dy * dy)));
+        xyzo[3 * i] = xyz[3 * i] + xyzn[3 * i] * wave;
+        xyzo[3 * i + 1] = xyz[3 * i + 1] + xyzn[3 * i + 1] * wave;
+        xyzo[3 * i + 2] = xyz[3 * i + 2] + xyzn[3 * i + 2] * wave;
     }
 }
 

@@ -44,6 +44,7 @@ def lib() -> C.CDLL:
         L.oracle_blur5x5.argtypes = [vp, vp, vp, ll, ll]
         L.oracle_sobel.argtypes = [vp, vp, vp, ll, ll]
         L.oracle_histogram.argtypes = [vp, vp, ll, ll]
+        L.oracle_wave_equation.argtypes = [vp, vp, vp, vp, ll, ll]
         _lib = L
     return _lib
 
@@ -126,6 +127,12 @@ def sobel(img, out, dims, offset=0, count=-1):
 def histogram(img, hist, offset=0, count=-1):
     lib().oracle_histogram(_p(img), _p(hist), offset, img.size - offset if count < 0 else count)
     return hist
+
+
+def wave_equation(xyz, xyzn, xyzo, arguments, offset=0, count=-1):
+    n = xyz.size // 3
+    lib().oracle_wave_equation(_p(xyz), _p(xyzn), _p(xyzo), _p(arguments), offset, n - offset if count < 0 else count)
+    return xyzo
 
 
 def splitmix64(seed: int, n: int) -> np.ndarray:

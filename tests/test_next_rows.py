@@ -1,0 +1,76 @@
+"""the Unity sample's waveEquation kernel on arrays of structs (Kamera.cs:234-268, ClArray.cs:1058-1074),
+OpenCL-C idioms running unmodified through the NVRTC prelude, and the micro-benchmark device sorter (ClObjectApi.cs:1222-1244)."""
+import numpy as np
+import pytest
+
+import cekirdekler_b200 as ck
+from cekirdekler_b200 import kernels
+from oracle import pyoracle as po
+
+pytestmark = pytest.mark.gpu
+
+
+def test_wave_equation_on_wrapped_structs(gpus):
+    """Kamera.cs: Vector3[] vertices/normals wrapped as byte arrays (12 bytes per work-item), `arguments` a plain float array;
+    the kernel text is the reference's own; the oracle is the reference's CPU branch (Kamera.cs:213-218)."""
+    n = 224 * 256
+    rng = np.random.default_rng(7)
+    base = rng.uniform(-1, 1, (n, 3)).astype(np.float32)
+    normals = base / np.maximum(np.linalg.norm(base, axis=1, keepdims=True), 1e-6).astype(np.float32)
+    verts = np.zeros((n, 3), np.float32)
+    xyz, xyzn, xyzo = ck.ClArray.wrapArrayOfStructs(base), ck.ClArray.wrapArrayOfStructs(normals), ck.ClArray.wrapArrayOfStructs(verts)
+    assert xyz.numberOfElementsPerWorkItem == 12 and xyz.Length == n * 12
+    args_h = np.zeros(64, np.float32)
+    arguments = ck.ClArray(args_h)
+    arguments.write, arguments.partialRead = False, False          # Kamera.cs:255
+    for a in (xyz, xyzn):
+        a.partialRead, a.read, a.write = True, False, False
+    xyzo.read = False
+    cr = ck.ClNumberCruncher(ck.ClPlatforms.all().gpus(), kernels.REFERENCE_WAVE_EQUATION)
+    assert cr.errorCode() == 0, cr.errorMessage()
+    for frame in range(4):
+        args_h[:5] = [1.0 + 0.1 * frame, 0.05 * frame, base[0, 0], base[0, 1], n]
+        assert xyz.nextParam(xyzn, xyzo, arguments).compute(cr, 1, "waveEquation", n, 64) == 0
+        exp = np.zeros((n, 3), np.float32)
+        po.wave_equation(base.reshape(-1), normals.reshape(-1), exp.reshape(-1), args_h)
+        assert np.allclose(verts, exp, rtol=0, atol=2e-5), np.abs(verts - exp).max()
+
+
+def test_opencl_c_idioms_run(gpus):
+    src = """
+    float helper(float x) { return mad(x, 2.0f, 1.0f); }
+    __kernel void idioms(__global const float* in, __global float* out, __global int* hist)
+    {
+        __local float tile[256];
+        int l = get_local_id(0);
+        int i = get_global_id(0);
+        tile[l] = in[i];
+        barrier(CLK_LOCAL_MEM_FENCE);
+        float left = tile[(l + get_local_size(0) - 1) % get_local_size(0)];
+        float4 v = make_float4(tile[l], left, 1.0f, 0.0f);
+        v = v * 2.0f + v;
+        out[i] = helper(dot(v, v)) + (float)(get_group_id(0) % 2);
+        atomic_add(&hist[i % 16], 1);
+    }"""
+    n = 1 << 14
+    cr = ck.ClNumberCruncher(ck.ClPlatforms.all().gpus(), src)
+    assert cr.errorCode() == 0, cr.errorMessage()
+    a, out, hist = ck.ClArray(n, np.float32), ck.ClArray(n, np.float32), ck.ClArray(16, np.int32)
+    a.view[:] = np.arange(n) % 17
+    a.readOnly = True
+    out.writeOnly = True
+    hist.writeAll = True
+    assert a.nextParam(out, hist).compute(cr, 1, "idioms", n, 256) == 0
+    x = a.view.reshape(-1, 256)
+    left = np.roll(x, 1, axis=1)
+    v2 = (3 * x) ** 2 + (3 * left) ** 2 + 9.0
+    group = (np.arange(n) // 256 % 2).reshape(-1, 256)
+    assert np.allclose(out.view.reshape(-1, 256), v2 * 2 + 1 + group, rtol=1e-6)
+    if gpus == 1:
+        assert hist.view.sum() == n and (hist.view == n // 16).all()
+
+
+def test_devices_sorted_by_nbody_micro_benchmark(gpus):
+    devs = ck.ClPlatforms.all().gpus()
+    ranked = devs.devicesWithHighestDirectNbodyPerformance(4096)
+    assert sorted(ranked.ordinals) == sorted(devs.ordinals)

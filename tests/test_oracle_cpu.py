@@ -129,6 +129,25 @@ def test_image_oracles():
     assert np.allclose(s.reshape(H, W)[5, 5:-5], 8.0 / W)   # |gx| = 8 * slope in the interior
 
 
+def test_wave_equation_matches_the_reference_cpu_branch_in_float64():
+    """Kamera.cs:213-218: v = v0 + n * 0.02*ctr*sin(40t + 100*sqrt(dx^2+dy^2)) — restated here in float64 numpy."""
+    n = 4096
+    rng = np.random.default_rng(3)
+    base = rng.uniform(-1, 1, (n, 3)).astype(np.float32)
+    nor = rng.uniform(-1, 1, (n, 3)).astype(np.float32)
+    out = np.zeros((n, 3), np.float32)
+    args = np.zeros(64, np.float32)
+    args[:5] = [1.25, 0.3, 0.2, -0.4, n]
+    po.wave_equation(base.reshape(-1), nor.reshape(-1), out.reshape(-1), args)
+    dx, dy = base[:, 0].astype(np.float64) - np.float64(args[2]), base[:, 1].astype(np.float64) - np.float64(args[3])
+    wave = 0.02 * 1.25 * np.sin(40.0 * np.float64(args[1]) + 100.0 * np.sqrt(dx * dx + dy * dy))
+    assert np.allclose(out, base + nor * wave[:, None], rtol=0, atol=3e-6)
+    args[4] = n // 2                                     # the kernel's own guard: work-items >= n leave the output alone
+    out2 = np.full((n, 3), 7.0, np.float32)
+    po.wave_equation(base.reshape(-1), nor.reshape(-1), out2.reshape(-1), args)
+    assert np.array_equal(out2[: n // 2], out[: n // 2]) and (out2[n // 2:] == 7.0).all()
+
+
 def test_splitmix_stream_is_deterministic():
     a, b = po.uniform(0xC0FFEE, 1000, -15, 15), po.uniform(0xC0FFEE, 1000, -15, 15)
     assert np.array_equal(a, b) and a.min() >= -15 and a.max() < 15 and abs(float(a.mean())) < 1.5

@@ -49,6 +49,7 @@ def test_shipped_kernels_build_for_sm_100a(name):
 @pytest.mark.parametrize("src", [
     kernels.reference_copy_kernel("uchar"), kernels.reference_copy_kernel("double"), kernels.reference_copy_kernel("long"),
     kernels.REFERENCE_COPY_KERNEL_CHAR, kernels.REFERENCE_VECTOR_ADD, kernels.reference_nbody_kernel(8192),
+    kernels.REFERENCE_WAVE_EQUATION,
 ])
 def test_reference_opencl_strings_build_unmodified(src):
     rc, log, _ = compile_check(src)
