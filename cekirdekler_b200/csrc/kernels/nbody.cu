@@ -303,3 +303,226 @@ __kernel void nBody3Dq(const float4* __restrict__ pos, float4* __restrict__ vel,
         posOut[i] = make_float4(__fmaf_rn(v.x, dt, pi.x), __fmaf_rn(v.y, dt, pi.y), __fmaf_rn(v.z, dt, pi.z), pi.w);
     }
 }
+
+// nBody3Dw — the same step scheduled through a device-side work queue, so that the time of a launch does not depend on how
+// the launch geometry happens to divide over 148 SMs.  With one equal slab of work per work-group (nBody3D) a device's share
+// of 131072 / D bodies gives 1024 / D work-groups for 592 resident slots: 1.73, 0.86, 0.43 ... waves, i.e. 13-57 % of the
+// SM-time idle in the tail (ncu on nBody3D, round 1: 13.3 of 16 warps active on average).  Here the work is cut into UNITS
+//     unit (g, c) = bodies [128 g, 128 g + 128) of the share  x  j tiles [c T, c T + T),   T = NBW_TILES_PER_WARP * warps,
+// and every work-group pulls units from a counter until none are left (work-groups scheduled after that exit at once).
+// A unit is computed like a work-group of nBody3D (lane q carries bodies 4q..4q+3, warp w sweeps its share of the tiles,
+// packed pair arithmetic), its 128 x 3 partial accelerations go to `scratch`, and the work-group that completes the LAST
+// unit of a body group adds the partials in chunk order and integrates the group.  Sums therefore do not depend on timing,
+// nor on how the bodies are split over devices (T depends on n and the work-group size only) — unless scratch is too small
+// for that chunking, in which case chunks are widened to fit.
+//   arguments   pos (whole `read`), vel, posOut (sliced; numberOfElementsPerWorkItem = 4 / workItemsPerBody floats),
+//               params = { dt, eps2, n, workItemsPerBody (1, 2 or 4), scratch capacity in units of 1024 floats },
+//               scratch: float array with read = write = false (device-resident, zeroed when the buffer is created).
+//   geometry    global range = workItemsPerBody * bodies; work-group size a multiple of 32 up to 256 (128 measured best).
+//               More work-items per body only means more resident work-groups to pull units: with 4 an 8-way split of
+//               131072 bodies still launches 512 work-groups per device.
+//   scratch     [0] next unit, [1] work-groups that left, [4 .. 4+G) units done per body group, then G*C*384 floats of
+//               partials (G = groups of the share, C = chunks); 131072 bodies on one device: C = 64, 100.7 MB.  The kernel
+//               leaves all counters at zero again.  One launch at a time per scratch array: do not use it from pipelined
+//               computes (blobs > 1) or from two computeIds at once.
+// Measured on B200 (build/exp/nb3.cu, round 1), GInter/s for a share of 131072 / 65536 / 32768 / 16384 bodies:
+//   nBody3D 2200 / 1791 / 1578 / 882;  this kernel 2591 / 2580 / 2536 / 2465 (69.6 % of the FP32 peak on a whole device).
+#define NBW_GROUP 128            // bodies per unit: 32 lanes x NB_B
+#define NBW_MAXW 8               // warps per work-group at most
+#define NBW_HDR 4                // ints before the per-group counters
+#define NBW_TILES_PER_WARP 2     // j tiles a warp sweeps per unit
+
+__kernel void nBody3Dw(const float4* __restrict__ pos, float4* __restrict__ vel, float4* __restrict__ posOut,
+                       const float* __restrict__ params, float* __restrict__ scratch)
+{
+    __shared__ float4 sA[NBW_MAXW][NB_TILE / 2];
+    __shared__ float4 sB[NBW_MAXW][NB_TILE / 2];
+    __shared__ float red[NBW_MAXW - 1][3 * NB_B][32];
+    __shared__ int sNext, sLast;
+    const float dt = __ldg(params + 0), eps2 = __ldg(params + 1);
+    const int n = (int)__ldg(params + 2);
+    const int wpb = (int)__ldg(params + 3);
+    const long long cap = (long long)__ldg(params + 4) * 1024;
+    const int S = blockDim.x >> 5, warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int firstBody = (int)(get_global_offset(0) / wpb);
+    const int share = (int)((long long)gridDim.x * blockDim.x / wpb);
+    const int lastBody = firstBody + share - 1;
+    const int G = (share + NBW_GROUP - 1) / NBW_GROUP;
+    const int tiles = (n + NB_TILE - 1) / NB_TILE;
+    int* ctr = reinterpret_cast<int*>(scratch);
+    int* done = ctr + NBW_HDR;
+    const long long P0 = ((long long)(NBW_HDR + G) + 127) / 128 * 128;
+    // chunking: T tiles per unit; widened (in whole multiples of the warp count) only if scratch cannot hold G*C partial sets
+    int T = NBW_TILES_PER_WARP * S;
+    int C = (tiles + T - 1) / T;
+    {
+        const long long cfit = (cap - P0) / ((long long)G * 3 * NBW_GROUP);
+        if (cfit < 1 || S < 1 || S > NBW_MAXW || share < NB_B) {
+            if (blockIdx.x == 0 && threadIdx.x == 0)
+                printf("nBody3Dw: scratch holds %lld floats, needs at least %lld; work-group size %d must be 32..256\n", cap,
+                       P0 + (long long)G * 3 * NBW_GROUP, (int)blockDim.x);
+            return;
+        }
+        if (C > cfit) {
+            T = (int)(((tiles + cfit - 1) / cfit + S - 1) / S) * S;
+            C = (tiles + T - 1) / T;
+        }
+    }
+    const int totalUnits = G * C;
+    float* part = scratch + P0;
+    const ck_f32x2 EPS = ck_pack(eps2, eps2);
+    float* fA = reinterpret_cast<float*>(sA[warp]);
+    float* fB = reinterpret_cast<float*>(sB[warp]);
+    const float4* tA = sA[warp];
+    const float4* tB = sB[warp];
+
+    // The work-group always knows its NEXT unit as well as the current one (it draws two tickets at the start and one
+    // per finished unit), so the first j tile of the next unit is prefetched while the last tile of this one is consumed.
+    float4 nxt[NB_PREFETCH];
+    auto fetchTile = [&](int tile, bool live) {
+#pragma unroll
+        for (int k = 0; k < NB_PREFETCH; k++) {
+            const int j = tile * NB_TILE + lane + 32 * k;
+            nxt[k] = (live && j < n) ? pos[j] : make_float4(0.0f, 0.0f, 0.0f, 0.0f);   // padding bodies have mass 0
+        }
+    };
+    const int per = T / S;
+    auto warpTiles = [&](int unit, int& first, int& end) {   // this warp's tiles of the unit's chunk
+        const int c = unit % C;
+        const int chunkEnd = min(c * T + T, tiles);
+        first = min(c * T + warp * per, chunkEnd);
+        end = min(first + per, chunkEnd);
+    };
+    if (threadIdx.x == 0) {
+        sNext = atomicAdd(&ctr[0], 1);
+        sLast = atomicAdd(&ctr[0], 1);
+    }
+    __syncthreads();
+    int u = sNext, un = sLast;
+    __syncthreads();
+    int t0 = 0, t1 = 0, gLoaded = -1;
+    if (u < totalUnits) warpTiles(u, t0, t1);
+    fetchTile(t0, t0 < t1);
+    ck_f32x2 PIX[NB_B], PIY[NB_B], PIZ[NB_B], AX[NB_B], AY[NB_B], AZ[NB_B];
+    while (u < totalUnits) {
+        const int g = u / C;
+        if (g != gLoaded) {   // consecutive units mostly stay in one body group
+            int i0 = firstBody + g * NBW_GROUP + NB_B * lane;
+            if (i0 > lastBody) i0 = lastBody - (NB_B - 1);   // lanes past a ragged last group recompute live bodies; nothing of theirs is used
+#pragma unroll
+            for (int b = 0; b < NB_B; b++) {
+                const float4 p = pos[i0 + b];
+                PIX[b] = ck_pack(p.x, p.x);
+                PIY[b] = ck_pack(p.y, p.y);
+                PIZ[b] = ck_pack(p.z, p.z);
+            }
+            gLoaded = g;
+        }
+#pragma unroll
+        for (int b = 0; b < NB_B; b++) {
+            AX[b] = ck_pack(0.0f, 0.0f);
+            AY[b] = AX[b];
+            AZ[b] = AX[b];
+        }
+        int n0 = 0, n1 = 0;
+        if (un < totalUnits) warpTiles(un, n0, n1);
+        if (t0 >= t1) fetchTile(n0, n0 < n1);   // a short last chunk left this warp nothing: go straight to the next unit's tile
+        for (int tile = t0; tile < t1; tile++) {
+#pragma unroll
+            for (int k = 0; k < NB_PREFETCH; k++) {
+                const int t = lane + 32 * k;
+                const int p = t >> 1, h = t & 1;
+                fA[p * 4 + h] = nxt[k].x;
+                fA[p * 4 + 2 + h] = nxt[k].y;
+                fB[p * 4 + h] = nxt[k].z;
+                fB[p * 4 + 2 + h] = nxt[k].w;
+            }
+            __syncwarp();
+            if (tile + 1 < t1) fetchTile(tile + 1, true);
+            else fetchTile(n0, n0 < n1);
+            // unroll 4: with 2 the loop-carried accumulators cost 16 register moves per iteration (SASS, round 1)
+#pragma unroll 4
+            for (int t = 0; t < NB_TILE / 2; t++) {
+                const float4 a = tA[t], b4 = tB[t];
+                const ck_f32x2 PX = ck_pack(a.x, a.y), PY = ck_pack(a.z, a.w), PZ = ck_pack(b4.x, b4.y), PM = ck_pack(b4.z, b4.w);
+#pragma unroll
+                for (int b = 0; b < NB_B; b++) NB_PAIR_INTERACT(PIX[b], PIY[b], PIZ[b], AX[b], AY[b], AZ[b])
+            }
+            __syncwarp();
+        }
+        float acc[3 * NB_B];
+#pragma unroll
+        for (int b = 0; b < NB_B; b++) {
+            float lo, hi;
+            ck_unpack(AX[b], lo, hi); acc[3 * b] = lo + hi;
+            ck_unpack(AY[b], lo, hi); acc[3 * b + 1] = lo + hi;
+            ck_unpack(AZ[b], lo, hi); acc[3 * b + 2] = lo + hi;
+        }
+        if (warp > 0) {
+#pragma unroll
+            for (int k = 0; k < 3 * NB_B; k++) red[warp - 1][k][lane] = acc[k];
+        }
+        __syncthreads();
+        if (warp == 0) {
+            for (int s = 0; s < S - 1; s++) {   // fixed order: warp 1, 2, ...
+#pragma unroll
+                for (int k = 0; k < 3 * NB_B; k++) acc[k] += red[s][k][lane];
+            }
+            float* dst = part + (long long)u * (3 * NBW_GROUP);
+#pragma unroll
+            for (int b = 0; b < NB_B; b++) {
+                __stcg(dst + 0 * NBW_GROUP + b * 32 + lane, acc[3 * b]);
+                __stcg(dst + 1 * NBW_GROUP + b * 32 + lane, acc[3 * b + 1]);
+                __stcg(dst + 2 * NBW_GROUP + b * 32 + lane, acc[3 * b + 2]);
+            }
+            __threadfence();
+            __syncwarp();
+            if (lane == 0) {
+                sLast = (atomicAdd(&done[g], 1) == C - 1);
+                sNext = atomicAdd(&ctr[0], 1);
+            }
+        }
+        __syncthreads();
+        const bool last = sLast != 0;
+        const int unext = sNext;
+        if (last) {
+            // every unit of group g has published its partials (fence before the counter, fence after it here)
+            __threadfence();
+            for (int t = threadIdx.x; t < NBW_GROUP; t += blockDim.x) {
+                const int body = firstBody + g * NBW_GROUP + NB_B * (t & 31) + (t >> 5);
+                if (body <= lastBody) {
+                    float ax = 0.0f, ay = 0.0f, az = 0.0f;
+                    const float* src = part + (long long)g * C * (3 * NBW_GROUP) + t;
+#pragma unroll 8
+                    for (int cc = 0; cc < C; cc++) {
+                        ax += __ldcg(src + 0 * NBW_GROUP);
+                        ay += __ldcg(src + 1 * NBW_GROUP);
+                        az += __ldcg(src + 2 * NBW_GROUP);
+                        src += 3 * NBW_GROUP;
+                    }
+                    const float4 p = pos[body];
+                    float4 v = vel[body];
+                    v.x = __fmaf_rn(ax, dt, v.x);
+                    v.y = __fmaf_rn(ay, dt, v.y);
+                    v.z = __fmaf_rn(az, dt, v.z);
+                    vel[body] = v;
+                    posOut[body] = make_float4(__fmaf_rn(v.x, dt, p.x), __fmaf_rn(v.y, dt, p.y), __fmaf_rn(v.z, dt, p.z), p.w);
+                }
+            }
+            if (threadIdx.x == 0) done[g] = 0;
+        }
+        __syncthreads();
+        u = un;
+        un = unext;
+        t0 = n0;
+        t1 = n1;
+    }
+    // the last work-group to leave re-arms the queue for the next launch (every work-group draws its tickets before it
+    // leaves, and leaves once)
+    if (threadIdx.x == 0) {
+        if (atomicAdd(&ctr[1], 1) == (int)gridDim.x - 1) {
+            ctr[0] = 0;
+            ctr[1] = 0;
+        }
+    }
+}

@@ -274,6 +274,72 @@ def test_nbody3d_positions_within_1e4_relative(gpus, n, steps, kernel, items_per
         assert np.allclose(got[:4], ref, rtol=1e-4, atol=1e-6)
 
 
+def run_nbody3dw(devs, pos0, steps, wpb, local, scratch_kfloats=None, balance_steps=0):
+    """nBody3Dw through compute(): scratch is a device-resident array (no read, no write); returns positions and velocities."""
+    n = pos0.shape[0]
+    cr = ck.ClNumberCruncher(devs, kernels.source("nbody"))
+    assert cr.errorCode() == 0, cr.errorMessage()
+    groups, chunks = (n + 127) // 128 + 8, ((n + 255) // 256 + 2 * (local // 32) - 1) // (2 * (local // 32))
+    kfloats = scratch_kfloats if scratch_kfloats is not None else (groups * chunks * 384 + groups + 256 + 1023) // 1024
+    pa, pb, vel, params, scratch = (ck.ClFloatArray(4 * n), ck.ClFloatArray(4 * n), ck.ClFloatArray(4 * n), ck.ClFloatArray(8),
+                                    ck.ClFloatArray(kfloats * 1024))
+    pa.view[:] = pos0.reshape(-1)
+    params.view[:5] = [1e-3, 1e-4, n, wpb, kfloats]
+    params.readOnly = True
+    scratch.read, scratch.write = False, False
+    vel.partialRead, vel.read = True, False
+    for arr in (pa, pb, vel):
+        arr.numberOfElementsPerWorkItem = 4 // wpb
+    src, dst = pa, pb
+    for _ in range(steps):
+        src.read, src.partialRead, src.write = True, False, False
+        dst.read, dst.partialRead, dst.write = False, False, True
+        assert src.nextParam(vel, dst, params, scratch).compute(cr, 1, "nBody3Dw", n * wpb, local) == 0
+        src, dst = dst, src
+    out = src.view.reshape(n, 4).copy(), vel.view.reshape(n, 4).copy()
+    for a in (pa, pb, vel, params, scratch):
+        a.dispose()
+    cr.dispose()
+    return out
+
+
+@pytest.mark.parametrize("wpb,local", [(1, 128), (4, 128), (4, 256), (2, 64), (4, 32)])
+@pytest.mark.parametrize("n,steps", [(2048, 1), (16384, 10), (8192 + 512, 3)])
+def test_nbody3d_work_queue_positions_within_1e4_relative(gpus, n, steps, wpb, local):
+    """Ten steps in a row also prove that the kernel re-arms its own queue; 8704 bodies leave ragged groups and a short last chunk."""
+    pos0 = nbody3d_inputs(n)
+    params_h = np.array([1e-3, 1e-4, n, 0], np.float32)
+    p, v, o = pos0.copy().reshape(-1), np.zeros(4 * n, np.float32), np.zeros(4 * n, np.float32)
+    for _ in range(steps):
+        po.nbody3d_step(p, v, o, params_h)
+        p, o = o, p
+    got, vel = run_nbody3dw(all_gpus(), pos0, steps, wpb, local)
+    exp = p.reshape(n, 4)
+    rel = np.abs(got[:, :3] - exp[:, :3]) / np.maximum(np.abs(exp[:, :3]), 1e-3)
+    assert rel.max() <= 1e-4, rel.max()
+    assert np.array_equal(got[:, 3], exp[:, 3])
+    vrel = np.abs(vel[:, :3] - v.reshape(n, 4)[:, :3]).max() / np.abs(v.reshape(n, 4)[:, :3]).max()
+    assert vrel <= 1e-4, vrel
+
+
+def test_nbody3d_work_queue_is_split_independent_and_fits_small_scratch(gpus):
+    """Partials are added in chunk order, and the chunking depends on n and the work-group size only: the same bits come out
+    whether one device or all of them share the bodies.  A scratch array too small for that chunking widens the chunks
+    (different rounding, same tolerance); one that cannot hold a single partial set per group makes the kernel refuse."""
+    n = 16384
+    pos0 = nbody3d_inputs(n)
+    one, vone = run_nbody3dw(all_gpus()[0], pos0, 3, 4, 128)
+    many, vmany = run_nbody3dw(all_gpus(), pos0, 3, 4, 128)
+    assert np.array_equal(one, many) and np.array_equal(vone, vmany)
+    again, _ = run_nbody3dw(all_gpus(), pos0, 3, 4, 128)
+    assert np.array_equal(many, again)
+    small, _ = run_nbody3dw(all_gpus()[0], pos0, 3, 4, 128, scratch_kfloats=(136 * 3 * 384 + 1023) // 1024 + 1)   # room for 3 chunks, not 8
+    rel = np.abs(small[:, :3] - one[:, :3]) / np.maximum(np.abs(one[:, :3]), 1e-3)
+    assert 0 < rel.max() <= 1e-4
+    refused, _ = run_nbody3dw(all_gpus()[0], pos0, 1, 4, 128, scratch_kfloats=8)
+    assert not refused.any()                                                    # untouched output, message on the device's stdout
+
+
 # ------------------------------------------------------------------ blur → Sobel → histogram (K5)
 @pytest.mark.parametrize("W,H", [(256, 128), (3840, 2160)])
 def test_image_chain_bit_exact(gpus, W, H):
