@@ -81,6 +81,7 @@ def shim() -> C.CDLL:
             "ckHostRegister": (i32, [vp, u64]), "ckHostUnregister": (i32, [vp]), "ckZeroBuffer": (i32, [vp, vp]),
             "ckBroadcastUpload": (i32, [C.POINTER(vp), C.POINTER(vp), i32, vp]),
             "ckBroadcastCounts": (None, [C.POINTER(u64), C.POINTER(u64)]),
+            "ckNBody3DStepNoAlloc": (i32, [i32, vp, vp, vp, vp, i32, i32, i32, C.c_float, C.c_float]),
         }
         for name, (res, args) in sig.items():
             fn = getattr(L, name)

@@ -203,6 +203,25 @@ int32_t   ckBroadcastUpload(ck_handle* hQueues, ck_handle* hBuffers, int32_t nDe
 /* How many broadcasts went through NCCL and through peer-copy trees since the library was loaded. */
 void      ckBroadcastCounts(uint64_t* viaNccl, uint64_t* viaPeerCopies);
 
+/* One n-body step (the nBody3Dw kernel: a += m d / (|d|^2 + eps2)^1.5 over all n bodies, v += a dt, posOut = p + v dt)
+ * for bodies [firstBody, firstBody + bodies), WITHOUT allocating anything.  This one has no counterpart in the reference:
+ * there every kernel argument is a buffer made by createBuffer, and making a buffer is a cudaMalloc, which drains every
+ * queue of the GPU and can fail.  It is for callers that cannot accept either — code that runs while an enqueue-mode
+ * region, a pipeline or a device pool keeps the same GPU's queues busy, and hosts whose device memory already belongs to
+ * another allocator.  The kernel's work queue and partial sums live in a 16 MiB array inside the library's device image
+ * (held by every GPU that loads the library, until exit) instead of a caller-made scratch buffer.
+ *   pos, vel, posOut   DEVICE pointers to n float4 each (e.g. ckBufferDevicePointer); pos is read whole, vel and posOut
+ *                      are read/written for the share only.  stream is a cudaStream_t (e.g. ckQueueStream) on `device`.
+ *   limits             bodies: a positive multiple of 32, at most 1,048,576 per call; n at most 16,777,216.
+ *   returns            0 enqueued (the call does not wait), 1 bad argument, 2 beyond the limits (nothing launched),
+ *                      3 CUDA error; ckGetLastError() has the text.
+ *   first call         on each device looks up the array's address; make it before starting any stream capture.
+ *   sharing            every call on a device uses the same array and clears the counters it needs first, in stream
+ *                      order.  Calls whose kernels may overlap on the GPU (different streams, no event between them)
+ *                      race on it: keep a device's calls on one stream or order them with events. */
+int32_t   ckNBody3DStepNoAlloc(int32_t device, void* stream, const void* pos, void* vel, void* posOut, int32_t n,
+                               int32_t firstBody, int32_t bodies, float dt, float eps2);
+
 #ifdef __cplusplus
 }
 #endif
