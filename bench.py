@@ -379,6 +379,7 @@ def bench_nbody(ck, kernels, po, devs, pk, sms, steps, warmup, spmd_attach=None,
     n = 131072
     cr = ck.ClNumberCruncher(devs, kernels.source("nbody"))
     assert cr.errorCode() == 0, cr.errorMessage()
+    cr.balancerMode = 2
     if spmd_attach:
         spmd_attach(cr)
     pos = np.zeros((n, 4), np.float32)
@@ -489,7 +490,7 @@ def run_ours(args):
 
     cr = ck.ClNumberCruncher(devs, kernels.source("mandelbrot"))
     assert cr.errorCode() == 0, cr.errorMessage()
-    cr.balancerMode = 1 if args.balancer == "adaptive" else 0
+    cr.balancerMode = {"reference": 0, "adaptive": 1, "profile": 2}[args.balancer]
     if spmd_mode:
         spmd.attach(cr, rank, world, torch_dev)
     npix = W * H
@@ -555,15 +556,28 @@ def run_ours(args):
     value = npix / (ms_per_step * 1e-3) / 1e6
 
     # ---- leg 2: end to end through the public API with host buffers (view upload + slice download every step) ----
-    CID_E2E = CID_RES   # same compute id: the balanced split carries over from the resident leg
-    e2e_t = []
-    for i in range(args.warmup + args.steps):
+    # Its own compute id: with host buffers a device's time is max(its kernels, the download of its slice), so the balanced
+    # split is a different one (devices holding the cheap rows become host-link bound).  Settled like the resident leg.
+    CID_E2E = 2
+    e2e_t, e2e_imb, e2e_settle = [], [], 0
+
+    def step_e2e():
         barrier()
         t0 = time.perf_counter()
         assert g.compute(cr, CID_E2E, "mandelbrot", items, 256, 0, True, args.e2e_mode == "event", args.e2e_blobs) == 0
         dt = allmax(time.perf_counter() - t0)
-        if i >= args.warmup:
-            e2e_t.append(dt)
+        tt = cr_times(cr, CID_E2E, cr.benchmarks(CID_E2E), spmd_mode,
+                      allgather=(lambda v: gather(dist, torch, torch_dev, v, world)) if spmd_mode else None)
+        e2e_imb.append(max(tt) / (sum(tt) / len(tt)))
+        return dt
+
+    for _ in range(args.warmup):
+        step_e2e()
+    while n_gpus > 1 and e2e_settle < 16 and not (len(e2e_imb) >= 2 and max(e2e_imb[-2:]) <= 1.03):
+        step_e2e()
+        e2e_settle += 1
+    for _ in range(args.steps):
+        e2e_t.append(step_e2e())
     e2e_ms = float(np.mean(e2e_t)) * 1e3
     e2e_value = npix / (e2e_ms * 1e-3) / 1e6
 
@@ -628,7 +642,11 @@ def run_ours(args):
             "wall_ms_per_step": wall / args.steps * 1e3,
             "clocks": clk,
             "e2e": {"value": e2e_value, "unit": UNIT, "ms_per_step": e2e_ms, "h2d_bytes_per_step": 32 * n_gpus,
-                    "d2h_bytes_per_step": 4 * npix, "mode": f"{args.e2e_mode}-controlled pipeline, {args.e2e_blobs} blobs, pinned host arrays"},
+                    "d2h_bytes_per_step": 4 * npix, "mode": f"{args.e2e_mode}-controlled pipeline, {args.e2e_blobs} blobs, pinned host arrays",
+                    "balancer_settle_steps": e2e_settle,
+                    "balancer": {"iterations_to_converge": first_stable(e2e_imb) if n_gpus > 1 else 0,
+                                 "imbalance_max_over_mean": [round(v, 4) for v in e2e_imb],
+                                 "final_shares": [round(x / items, 4) for x in cr.globalRanges(CID_E2E)]}},
             "gpu_launches": launches,
             "roofline": roof,
             "cpu_baseline": line_cpu,
@@ -664,7 +682,7 @@ def main():
     ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--balancer", default="adaptive", choices=["adaptive", "reference"])
+    ap.add_argument("--balancer", default="profile", choices=["profile", "adaptive", "reference"])
     ap.add_argument("--no-all", dest="all", action="store_false", help="skip the SAXPY and n-body workloads")
     ap.add_argument("--e2e-blobs", type=int, default=16, help="pipeline blobs of the end-to-end leg (multiple of 4)")
     ap.add_argument("--e2e-mode", default="event", choices=["event", "driver"], help="pipelining mode of the end-to-end leg")

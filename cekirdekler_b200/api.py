@@ -94,6 +94,15 @@ class ClDevices:
     def devicesWithDedicatedMemory(self) -> "ClDevices":
         return ClDevices(self.ordinals, self.streamingEnabled)
 
+    def devicesWithHostMemorySharing(self) -> "ClDevices":  # ClObjectApi.cs:1170: iGPUs/CPUs only; every B200 has its own HBM
+        return ClDevices([], self.streamingEnabled)
+
+    def devicesWithHighestIntrapolatedNbodyPerformance(self) -> "ClDevices":  # ClObjectApi.cs:1254-1257 throws as well
+        raise NotImplementedError("not implemented in the reference either (ClObjectApi.cs:1256)")
+
+    def devicesWithHighestLeastOscillatedNbodyPerformance(self) -> "ClDevices":  # ClObjectApi.cs:1267-1270
+        raise NotImplementedError("not implemented in the reference either (ClObjectApi.cs:1269)")
+
     def devicesWithHighestDirectNbodyPerformance(self, n: int = 16 * 1024) -> "ClDevices":
         """Orders the devices by a direct n-body micro-benchmark, fastest first (ClObjectApi.cs:1222-1244 runs
         Tester.nBody(16K) on each device); here the 2-D reference kernel `nBody2D` at n bodies, timed on the device."""
@@ -434,7 +443,7 @@ class ClNumberCruncher:
     repeatCount = _prop(4)
     performanceFeed = _prop(5)
     smoothLoadBalancer = _prop(6)
-    balancerMode = _prop(7)       # 0 = reference arithmetic, 1 = adaptive window (quirk Q14 fixed)
+    balancerMode = _prop(7)       # 0 = reference arithmetic, 1 = adaptive window (quirk Q14 fixed), 2 = cost-profile partition
     deviceClock = _prop(8)        # 1 = CUDA-event timing for the balancer, 0 = host stopwatch like the reference
     broadcastWholeReads = _prop(9)
     del _prop

@@ -27,6 +27,69 @@ static long long sum(const std::vector<int>& a) {
     return s;
 }
 
+// Profile mode.  The reference's rule gives device i a share proportional to range_i / time_i: it treats the cost of a
+// work-item as a property of the DEVICE.  When the cost depends on the POSITION in the range (Mandelbrot rows), a device
+// that is handed more items gets its neighbour's items at the neighbour's cost, the linear extrapolation overshoots, and
+// the split oscillates (8 B200s, round 1: 16 calls to settle; one slow device among 8 never settles in simulation).
+// Here the measured times are read as a piecewise-constant cost density over the global range,
+//     density(x) = (time_i + 0.01) / range_i   for x in device i's segment,
+// and the new boundaries cut the integral of that density into equal parts; every call refines the density around the
+// current boundaries.  The move toward those boundaries is damped (0.8; 0.5 if the imbalance grew since the last call,
+// which is what a device-speed difference looks like to a position model; 0.3 once max/mean time <= 1.05 so timing noise
+// does not jitter a settled split).  Same snap-to-step and sum fix-up as the reference.
+static void profileBalance(const std::vector<double>& benchmark, BalanceState& st, int totalRange, std::vector<int>& ranges,
+                           int step) {
+    const int n = (int)ranges.size();
+    std::vector<double> len, dens;   // active segments in range order
+    double total = 0.0, mx = 0.0;
+    for (int i = 0; i < n; i++)
+        if (ranges[i] > 0) {
+            const double t = benchmark[i] + 0.01;
+            len.push_back((double)ranges[i]);
+            dens.push_back(t / (double)ranges[i]);
+            total += t;
+            mx = t > mx ? t : mx;
+        }
+    if (len.empty()) return;
+    const double imbalance = mx * (double)len.size() / total;
+    const double target = total / (double)n;
+    std::vector<double> want(n, 0.0);
+    size_t seg = 0;
+    double used = 0.0, assigned = 0.0;
+    for (int d = 0; d + 1 < n; d++) {
+        double need = target, length = 0.0;
+        while (seg < len.size()) {
+            const double avail = (len[seg] - used) * dens[seg];
+            if (avail >= need - 1e-15) {
+                const double take = dens[seg] > 0.0 ? need / dens[seg] : 0.0;
+                used += take;
+                length += take;
+                break;
+            }
+            need -= avail;
+            length += len[seg] - used;
+            seg++;
+            used = 0.0;
+        }
+        want[d] = length;
+        assigned += length;
+    }
+    want[n - 1] = (double)totalRange - assigned;
+
+    double gain = imbalance > 1.05 ? 0.8 : 0.3;
+    if (st.lastImbalance > 0.0 && imbalance > 1.02 * st.lastImbalance && imbalance > 1.05) gain = 0.5;
+    st.lastImbalance = imbalance;
+
+    for (int i = 0; i < n; i++) {
+        const int tmp = (int)((double)ranges[i] + gain * (want[i] - (double)ranges[i]));
+        const int rem = tmp % step;
+        ranges[i] = (rem < step / 2) ? tmp - rem : tmp + (step - rem);
+        if (ranges[i] < 0) ranges[i] = 0;
+    }
+    while (sum(ranges) > totalRange) ranges[maxIndex(ranges)] -= step;
+    while (sum(ranges) < totalRange) ranges[maxIndex(ranges)] += step;
+}
+
 void loadBalance(const std::vector<double>& benchmark, bool smooth, BalanceState& st, int totalRange,
                  std::vector<int>& ranges, int step, BalancerMode mode) {
     const int n = (int)ranges.size();
@@ -44,6 +107,11 @@ void loadBalance(const std::vector<double>& benchmark, bool smooth, BalanceState
         totalThroughput += thr[i];
     }
     if (totalThroughput <= 0.0000001) totalThroughput = 0.01;
+
+    if (mode == BalancerMode::Profile) {
+        profileBalance(benchmark, st, totalRange, ranges, step);
+        return;
+    }
 
     std::vector<double> normalized(n, 0.0);
     if (smooth) {

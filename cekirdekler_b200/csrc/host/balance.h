@@ -17,6 +17,8 @@ enum class BalancerMode {
     Adaptive = 1,   // same arithmetic, but the average only spans samples taken while the devices were balanced
                     // (max/mean time <= 1.05): a transient discards the window, so stale shares are never mixed in
                     // (SURVEY.md quirk Q14).  Follows the un-smoothed trajectory while converging, smooths after.
+    Profile = 2,    // reads the device times as a cost density over the range and cuts its integral into equal parts
+                    // (see profileBalance in balance.cpp): for work whose cost depends on the position in the range
 };
 
 struct BalanceState {

@@ -146,7 +146,7 @@ void ckh_cruncher_set(ckh_cruncher c, int32_t id, int32_t v) {
         case 4: cr.repeatCount = v; break;
         case 5: cr.performanceFeed = (v != 0); break;
         case 6: cr.setSmoothLoadBalancer(v != 0); break;
-        case 7: if (k) k->balancerMode = v ? BalancerMode::Adaptive : BalancerMode::Reference; break;
+        case 7: if (k) k->balancerMode = v == 2 ? BalancerMode::Profile : (v ? BalancerMode::Adaptive : BalancerMode::Reference); break;
         case 8: if (k) k->deviceClock = (v != 0); break;
         case 9: if (k) k->broadcastWholeReads = (v != 0); break;
     }
@@ -163,7 +163,7 @@ int32_t ckh_cruncher_get(ckh_cruncher c, int32_t id) {
         case 4: return cr.repeatCount;
         case 5: return cr.performanceFeed;
         case 6: return k && k->smoothLoadBalancer;
-        case 7: return k && k->balancerMode == BalancerMode::Adaptive;
+        case 7: return k ? (int)k->balancerMode : 0;
         case 8: return k && k->deviceClock;
         case 9: return k && k->broadcastWholeReads;
     }
@@ -236,7 +236,7 @@ int32_t ckh_compute(ckh_cruncher c, ckh_array* arrays, int32_t nArrays, int32_t 
 ckh_balancer ckh_balancer_create(int32_t devices, int32_t mode) {
     auto* b = new BalancerBox();
     b->devices = devices;
-    b->mode = mode ? BalancerMode::Adaptive : BalancerMode::Reference;
+    b->mode = mode == 2 ? BalancerMode::Profile : (mode ? BalancerMode::Adaptive : BalancerMode::Reference);
     b->st.reset(devices);
     return b;
 }

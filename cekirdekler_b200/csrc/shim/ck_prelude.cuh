@@ -84,22 +84,131 @@ template <typename T> __device__ __forceinline__ T atomic_max(volatile T* p, T v
 template <typename T> __device__ __forceinline__ T atomic_xchg(volatile T* p, T v) { return atomicExch((T*)p, v); }
 template <typename T> __device__ __forceinline__ T atomic_cmpxchg(volatile T* p, T c, T v) { return atomicCAS((T*)p, c, v); }
 
-// ---- float2/float4 component-wise operators (OpenCL vector arithmetic) ----
-__device__ __forceinline__ float2 operator+(float2 a, float2 b) { return make_float2(a.x + b.x, a.y + b.y); }
-__device__ __forceinline__ float2 operator-(float2 a, float2 b) { return make_float2(a.x - b.x, a.y - b.y); }
-__device__ __forceinline__ float2 operator*(float2 a, float2 b) { return make_float2(a.x * b.x, a.y * b.y); }
-__device__ __forceinline__ float2 operator*(float2 a, float s) { return make_float2(a.x * s, a.y * s); }
-__device__ __forceinline__ float2 operator*(float s, float2 a) { return make_float2(a.x * s, a.y * s); }
-__device__ __forceinline__ float4 operator+(float4 a, float4 b) { return make_float4(a.x + b.x, a.y + b.y, a.z + b.z, a.w + b.w); }
-__device__ __forceinline__ float4 operator-(float4 a, float4 b) { return make_float4(a.x - b.x, a.y - b.y, a.z - b.z, a.w - b.w); }
-__device__ __forceinline__ float4 operator*(float4 a, float4 b) { return make_float4(a.x * b.x, a.y * b.y, a.z * b.z, a.w * b.w); }
-__device__ __forceinline__ float4 operator*(float4 a, float s) { return make_float4(a.x * s, a.y * s, a.z * s, a.w * s); }
-__device__ __forceinline__ float4 operator*(float s, float4 a) { return make_float4(a.x * s, a.y * s, a.z * s, a.w * s); }
-__device__ __forceinline__ float4& operator+=(float4& a, float4 b) { a.x += b.x; a.y += b.y; a.z += b.z; a.w += b.w; return a; }
-__device__ __forceinline__ float4& operator-=(float4& a, float4 b) { a.x -= b.x; a.y -= b.y; a.z -= b.z; a.w -= b.w; return a; }
-__device__ __forceinline__ float  dot(float4 a, float4 b) { return a.x * b.x + a.y * b.y + a.z * b.z + a.w * b.w; }
-__device__ __forceinline__ float  dot(float2 a, float2 b) { return a.x * b.x + a.y * b.y; }
-__device__ __forceinline__ float  length(float4 a) { return sqrtf(dot(a, a)); }
-__device__ __forceinline__ float  length(float2 a) { return sqrtf(dot(a, a)); }
+// ---- vector types: component-wise operators, literals and geometric built-ins (OpenCL C 6.4, 6.12.5) ----
+// OpenCL's `(float4)(a, b, c, d)` literal is rewritten by the host side to make_float4(a, b, c, d); the overloads below add
+// the forms CUDA's make_* lack: one scalar replicated, an existing vector, and vectors mixed with scalars.
+#define CK_VEC2_OPS(V, S, OP)                                                                                            \
+    __device__ __forceinline__ V operator OP(V a, V b) { return make_##V(a.x OP b.x, a.y OP b.y); }                      \
+    __device__ __forceinline__ V operator OP(V a, S s) { return make_##V(a.x OP s, a.y OP s); }                          \
+    __device__ __forceinline__ V operator OP(S s, V a) { return make_##V(s OP a.x, s OP a.y); }                          \
+    __device__ __forceinline__ V& operator OP##=(V& a, V b) { a.x OP##= b.x; a.y OP##= b.y; return a; }                  \
+    __device__ __forceinline__ V& operator OP##=(V& a, S s) { a.x OP##= s; a.y OP##= s; return a; }
+#define CK_VEC3_OPS(V, S, OP)                                                                                            \
+    __device__ __forceinline__ V operator OP(V a, V b) { return make_##V(a.x OP b.x, a.y OP b.y, a.z OP b.z); }          \
+    __device__ __forceinline__ V operator OP(V a, S s) { return make_##V(a.x OP s, a.y OP s, a.z OP s); }                \
+    __device__ __forceinline__ V operator OP(S s, V a) { return make_##V(s OP a.x, s OP a.y, s OP a.z); }                \
+    __device__ __forceinline__ V& operator OP##=(V& a, V b) { a.x OP##= b.x; a.y OP##= b.y; a.z OP##= b.z; return a; }   \
+    __device__ __forceinline__ V& operator OP##=(V& a, S s) { a.x OP##= s; a.y OP##= s; a.z OP##= s; return a; }
+#define CK_VEC4_OPS(V, S, OP)                                                                                                        \
+    __device__ __forceinline__ V operator OP(V a, V b) { return make_##V(a.x OP b.x, a.y OP b.y, a.z OP b.z, a.w OP b.w); }          \
+    __device__ __forceinline__ V operator OP(V a, S s) { return make_##V(a.x OP s, a.y OP s, a.z OP s, a.w OP s); }                  \
+    __device__ __forceinline__ V operator OP(S s, V a) { return make_##V(s OP a.x, s OP a.y, s OP a.z, s OP a.w); }                  \
+    __device__ __forceinline__ V& operator OP##=(V& a, V b) { a.x OP##= b.x; a.y OP##= b.y; a.z OP##= b.z; a.w OP##= b.w; return a; } \
+    __device__ __forceinline__ V& operator OP##=(V& a, S s) { a.x OP##= s; a.y OP##= s; a.z OP##= s; a.w OP##= s; return a; }
+#define CK_VEC_FAMILY(B)                                                                                                 \
+    CK_VEC2_OPS(B##2, B, +) CK_VEC2_OPS(B##2, B, -) CK_VEC2_OPS(B##2, B, *) CK_VEC2_OPS(B##2, B, /)                      \
+    CK_VEC3_OPS(B##3, B, +) CK_VEC3_OPS(B##3, B, -) CK_VEC3_OPS(B##3, B, *) CK_VEC3_OPS(B##3, B, /)                      \
+    CK_VEC4_OPS(B##4, B, +) CK_VEC4_OPS(B##4, B, -) CK_VEC4_OPS(B##4, B, *) CK_VEC4_OPS(B##4, B, /)                      \
+    __device__ __forceinline__ B##2 operator-(B##2 a) { return make_##B##2(-a.x, -a.y); }                                \
+    __device__ __forceinline__ B##3 operator-(B##3 a) { return make_##B##3(-a.x, -a.y, -a.z); }                          \
+    __device__ __forceinline__ B##4 operator-(B##4 a) { return make_##B##4(-a.x, -a.y, -a.z, -a.w); }                    \
+    __device__ __forceinline__ B##2 make_##B##2(B s) { return make_##B##2(s, s); }                                       \
+    __device__ __forceinline__ B##3 make_##B##3(B s) { return make_##B##3(s, s, s); }                                    \
+    __device__ __forceinline__ B##4 make_##B##4(B s) { return make_##B##4(s, s, s, s); }                                 \
+    __device__ __forceinline__ B##2 make_##B##2(B##2 v) { return v; }                                                    \
+    __device__ __forceinline__ B##3 make_##B##3(B##3 v) { return v; }                                                    \
+    __device__ __forceinline__ B##4 make_##B##4(B##4 v) { return v; }                                                    \
+    __device__ __forceinline__ B##3 make_##B##3(B##2 v, B z) { return make_##B##3(v.x, v.y, z); }                        \
+    __device__ __forceinline__ B##3 make_##B##3(B x, B##2 v) { return make_##B##3(x, v.x, v.y); }                        \
+    __device__ __forceinline__ B##4 make_##B##4(B##2 v, B z, B w) { return make_##B##4(v.x, v.y, z, w); }                \
+    __device__ __forceinline__ B##4 make_##B##4(B x, B##2 v, B w) { return make_##B##4(x, v.x, v.y, w); }                \
+    __device__ __forceinline__ B##4 make_##B##4(B x, B y, B##2 v) { return make_##B##4(x, y, v.x, v.y); }                \
+    __device__ __forceinline__ B##4 make_##B##4(B##2 a, B##2 b) { return make_##B##4(a.x, a.y, b.x, b.y); }              \
+    __device__ __forceinline__ B##4 make_##B##4(B##3 v, B w) { return make_##B##4(v.x, v.y, v.z, w); }                   \
+    __device__ __forceinline__ B##4 make_##B##4(B x, B##3 v) { return make_##B##4(x, v.x, v.y, v.z); }
+CK_VEC_FAMILY(float)
+CK_VEC_FAMILY(double)
+CK_VEC_FAMILY(int)
+CK_VEC_FAMILY(uint)
+
+#define CK_GEOMETRY(B, SQRT, RSQRT)                                                                                      \
+    __device__ __forceinline__ B dot(B##2 a, B##2 b) { return a.x * b.x + a.y * b.y; }                                   \
+    __device__ __forceinline__ B dot(B##3 a, B##3 b) { return a.x * b.x + a.y * b.y + a.z * b.z; }                       \
+    __device__ __forceinline__ B dot(B##4 a, B##4 b) { return a.x * b.x + a.y * b.y + a.z * b.z + a.w * b.w; }           \
+    __device__ __forceinline__ B length(B##2 a) { return SQRT(dot(a, a)); }                                              \
+    __device__ __forceinline__ B length(B##3 a) { return SQRT(dot(a, a)); }                                              \
+    __device__ __forceinline__ B length(B##4 a) { return SQRT(dot(a, a)); }                                              \
+    __device__ __forceinline__ B distance(B##2 a, B##2 b) { return length(a - b); }                                      \
+    __device__ __forceinline__ B distance(B##3 a, B##3 b) { return length(a - b); }                                      \
+    __device__ __forceinline__ B distance(B##4 a, B##4 b) { return length(a - b); }                                      \
+    __device__ __forceinline__ B##2 normalize(B##2 a) { return a * RSQRT(dot(a, a)); }                                   \
+    __device__ __forceinline__ B##3 normalize(B##3 a) { return a * RSQRT(dot(a, a)); }                                   \
+    __device__ __forceinline__ B##4 normalize(B##4 a) { return a * RSQRT(dot(a, a)); }                                   \
+    __device__ __forceinline__ B##3 cross(B##3 a, B##3 b) {                                                              \
+        return make_##B##3(a.y * b.z - a.z * b.y, a.z * b.x - a.x * b.z, a.x * b.y - a.y * b.x);                         \
+    }                                                                                                                    \
+    __device__ __forceinline__ B##4 cross(B##4 a, B##4 b) {                                                              \
+        return make_##B##4(a.y * b.z - a.z * b.y, a.z * b.x - a.x * b.z, a.x * b.y - a.y * b.x, (B)0);                   \
+    }
+CK_GEOMETRY(float, sqrtf, rsqrtf)
+CK_GEOMETRY(double, sqrt, rsqrt)
+
+#define CK_MAP1(F, G)                                                                                                    \
+    __device__ __forceinline__ float2 F(float2 a) { return make_float2(G(a.x), G(a.y)); }                                \
+    __device__ __forceinline__ float3 F(float3 a) { return make_float3(G(a.x), G(a.y), G(a.z)); }                        \
+    __device__ __forceinline__ float4 F(float4 a) { return make_float4(G(a.x), G(a.y), G(a.z), G(a.w)); }
+#define CK_MAP2(F, G)                                                                                                    \
+    __device__ __forceinline__ float2 F(float2 a, float2 b) { return make_float2(G(a.x, b.x), G(a.y, b.y)); }            \
+    __device__ __forceinline__ float3 F(float3 a, float3 b) { return make_float3(G(a.x, b.x), G(a.y, b.y), G(a.z, b.z)); } \
+    __device__ __forceinline__ float4 F(float4 a, float4 b) { return make_float4(G(a.x, b.x), G(a.y, b.y), G(a.z, b.z), G(a.w, b.w)); }
+CK_MAP1(sqrt, sqrtf) CK_MAP1(rsqrt, rsqrtf) CK_MAP1(fabs, fabsf) CK_MAP1(floor, floorf) CK_MAP1(ceil, ceilf)
+CK_MAP1(exp, expf) CK_MAP1(log, logf) CK_MAP1(sin, sinf) CK_MAP1(cos, cosf) CK_MAP1(native_sqrt, __fsqrt_rn)
+CK_MAP1(native_rsqrt, rsqrtf) CK_MAP1(native_exp, __expf) CK_MAP1(native_log, __logf) CK_MAP1(native_sin, __sinf)
+CK_MAP1(native_cos, __cosf)
+CK_MAP2(fmin, fminf) CK_MAP2(fmax, fmaxf) CK_MAP2(min, fminf) CK_MAP2(max, fmaxf) CK_MAP2(pow, powf)
+__device__ __forceinline__ float2 mad(float2 a, float2 b, float2 c) { return make_float2(fmaf(a.x, b.x, c.x), fmaf(a.y, b.y, c.y)); }
+__device__ __forceinline__ float3 mad(float3 a, float3 b, float3 c) { return make_float3(fmaf(a.x, b.x, c.x), fmaf(a.y, b.y, c.y), fmaf(a.z, b.z, c.z)); }
+__device__ __forceinline__ float4 mad(float4 a, float4 b, float4 c) { return make_float4(fmaf(a.x, b.x, c.x), fmaf(a.y, b.y, c.y), fmaf(a.z, b.z, c.z), fmaf(a.w, b.w, c.w)); }
+__device__ __forceinline__ float4 fma(float4 a, float4 b, float4 c) { return mad(a, b, c); }
+__device__ __forceinline__ float2 clamp(float2 v, float lo, float hi) { return make_float2(clamp(v.x, lo, hi), clamp(v.y, lo, hi)); }
+__device__ __forceinline__ float3 clamp(float3 v, float lo, float hi) { return make_float3(clamp(v.x, lo, hi), clamp(v.y, lo, hi), clamp(v.z, lo, hi)); }
+__device__ __forceinline__ float4 clamp(float4 v, float lo, float hi) { return make_float4(clamp(v.x, lo, hi), clamp(v.y, lo, hi), clamp(v.z, lo, hi), clamp(v.w, lo, hi)); }
+__device__ __forceinline__ float2 mix(float2 a, float2 b, float t) { return a + (b - a) * t; }
+__device__ __forceinline__ float3 mix(float3 a, float3 b, float t) { return a + (b - a) * t; }
+__device__ __forceinline__ float4 mix(float4 a, float4 b, float t) { return a + (b - a) * t; }
+__device__ __forceinline__ float4 convert_float4(int4 v) { return make_float4((float)v.x, (float)v.y, (float)v.z, (float)v.w); }
+__device__ __forceinline__ float4 convert_float4(uint4 v) { return make_float4((float)v.x, (float)v.y, (float)v.z, (float)v.w); }
+__device__ __forceinline__ int4   convert_int4(float4 v) { return make_int4((int)v.x, (int)v.y, (int)v.z, (int)v.w); }
+__device__ __forceinline__ float2 convert_float2(int2 v) { return make_float2((float)v.x, (float)v.y); }
+__device__ __forceinline__ int2   convert_int2(float2 v) { return make_int2((int)v.x, (int)v.y); }
+
+// ---- vloadN / vstoreN (OpenCL C 6.12.7): element offset is in units of the vector ----
+__device__ __forceinline__ float2 vload2(size_t i, const float* p) { return make_float2(p[2 * i], p[2 * i + 1]); }
+__device__ __forceinline__ float3 vload3(size_t i, const float* p) { return make_float3(p[3 * i], p[3 * i + 1], p[3 * i + 2]); }
+__device__ __forceinline__ float4 vload4(size_t i, const float* p) { return make_float4(p[4 * i], p[4 * i + 1], p[4 * i + 2], p[4 * i + 3]); }
+__device__ __forceinline__ void vstore2(float2 v, size_t i, float* p) { p[2 * i] = v.x; p[2 * i + 1] = v.y; }
+__device__ __forceinline__ void vstore3(float3 v, size_t i, float* p) { p[3 * i] = v.x; p[3 * i + 1] = v.y; p[3 * i + 2] = v.z; }
+__device__ __forceinline__ void vstore4(float4 v, size_t i, float* p) { p[4 * i] = v.x; p[4 * i + 1] = v.y; p[4 * i + 2] = v.z; p[4 * i + 3] = v.w; }
+
+// ---- integer built-ins (OpenCL C 6.12.3) ----
+__device__ __forceinline__ int  mul24(int a, int b) { return __mul24(a, b); }
+__device__ __forceinline__ int  mad24(int a, int b, int c) { return __mul24(a, b) + c; }
+__device__ __forceinline__ uint mul24(uint a, uint b) { return __umul24(a, b); }
+__device__ __forceinline__ uint mad24(uint a, uint b, uint c) { return __umul24(a, b) + c; }
+__device__ __forceinline__ int  mul_hi(int a, int b) { return __mulhi(a, b); }
+__device__ __forceinline__ uint mul_hi(uint a, uint b) { return __umulhi(a, b); }
+__device__ __forceinline__ int  popcount(uint x) { return __popc(x); }
+__device__ __forceinline__ int  clz(uint x) { return __clz((int)x); }
+__device__ __forceinline__ uint rotate(uint x, uint r) { return __funnelshift_l(x, x, r); }
+__device__ __forceinline__ uint abs_diff(int a, int b) { return a > b ? (uint)a - (uint)b : (uint)b - (uint)a; }
+__device__ __forceinline__ float step(float edge, float x) { return x < edge ? 0.0f : 1.0f; }
+__device__ __forceinline__ float smoothstep(float e0, float e1, float x) {
+    const float t = clamp((x - e0) / (e1 - e0), 0.0f, 1.0f);
+    return t * t * (3.0f - 2.0f * t);
+}
+__device__ __forceinline__ float fract(float x) { return fminf(x - floorf(x), 0x1.fffffep-1f); }
+__device__ __forceinline__ float degrees(float r) { return r * 57.29577951308232f; }
+__device__ __forceinline__ float radians(float d) { return d * 0.017453292519943295f; }
+template <typename T> __device__ __forceinline__ T select(T a, T b, int c) { return c ? b : a; }
 
 #endif  // CK_PRELUDE_CUH

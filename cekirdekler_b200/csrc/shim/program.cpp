@@ -24,6 +24,28 @@ static const char* kPrelude =
 
 static bool ident_char(char c) { return std::isalnum((unsigned char)c) || c == '_'; }
 
+// If src[i..] reads `( <vector type> ) (` returns the length of that prefix (through the second parenthesis), else 0.
+static size_t vector_literal_prefix(const std::string& src, size_t i) {
+    static const char* bases[] = {"float", "double", "int", "uint", "char", "uchar", "short", "ushort"};
+    const size_t n = src.size();
+    size_t p = i + 1;
+    while (p < n && std::isspace((unsigned char)src[p])) p++;
+    size_t b = p;
+    while (p < n && ident_char(src[p])) p++;
+    if (p - b < 4 || p >= n) return 0;
+    const char width = src[p - 1];
+    if (width != '2' && width != '3' && width != '4') return 0;
+    bool known = false;
+    for (const char* base : bases) known = known || src.compare(b, p - 1 - b, base) == 0;
+    if (!known) return 0;
+    while (p < n && std::isspace((unsigned char)src[p])) p++;
+    if (p >= n || src[p] != ')') return 0;
+    p++;
+    while (p < n && std::isspace((unsigned char)src[p])) p++;
+    if (p >= n || src[p] != '(') return 0;
+    return p + 1 - i;
+}
+
 // Finds `kernel void name(` / `__kernel void name(` occurrences outside comments and rewrites them.
 std::string rewrite_kernels(const std::string& src, std::vector<std::pair<std::string, int>>* kernels_out) {
     std::string out;
@@ -53,6 +75,22 @@ std::string rewrite_kernels(const std::string& src, std::vector<std::pair<std::s
             out.append(src, i, e - i);
             i = e;
             continue;
+        }
+        // OpenCL C vector literal `(float4)(a, b, c, d)` → `make_float4(a, b, c, d)`; the prelude adds the broadcast and
+        // mixed scalar/vector overloads OpenCL allows.  `(float4)x` (no second parenthesis) is left alone.
+        if (src[i] == '(') {
+            size_t len = vector_literal_prefix(src, i);
+            if (len) {
+                size_t b = i + 1;
+                while (std::isspace((unsigned char)src[b])) b++;
+                size_t e = b;
+                while (ident_char(src[e])) e++;
+                out += "make_";
+                out.append(src, b, e - b);
+                out.push_back('(');
+                i += len;
+                continue;
+            }
         }
         // candidate token start?
         bool at_token_start = (i == 0) || !ident_char(src[i - 1]);

@@ -52,7 +52,7 @@ const char* ckh_cruncher_device_name(ckh_cruncher c, int32_t i);     /* :296-299
 int32_t     ckh_cruncher_num_kernels(const char* kernelString);      /* kernel-name regex, :219-228 */
 const char* ckh_cruncher_kernel_name(const char* kernelString, int32_t i);
 /* property ids: 0 enqueueMode, 1 enqueueModeAsyncEnable, 2 noComputeMode, 3 fineGrainedQueueControl, 4 repeatCount,
- *   5 performanceFeed, 6 smoothLoadBalancer, 7 balancerMode (0 reference, 1 adaptive), 8 deviceClock,
+ *   5 performanceFeed, 6 smoothLoadBalancer, 7 balancerMode (0 reference, 1 adaptive, 2 profile), 8 deviceClock,
  *   9 broadcastWholeReads                                            ClNumberCruncher.cs:66-187 */
 void        ckh_cruncher_set(ckh_cruncher c, int32_t propId, int32_t value);
 int32_t     ckh_cruncher_get(ckh_cruncher c, int32_t propId);
@@ -83,7 +83,7 @@ int32_t ckh_compute(ckh_cruncher c, ckh_array* arrays, int32_t nArrays, int32_t 
 
 /* ---- Functions.loadBalance (pure host arithmetic) -------------------- HelperFunctions.cs:190-280, Cores.cs:569-605 */
 typedef void* ckh_balancer;
-ckh_balancer ckh_balancer_create(int32_t devices, int32_t mode /* 0 reference, 1 adaptive */);
+ckh_balancer ckh_balancer_create(int32_t devices, int32_t mode /* 0 reference, 1 adaptive, 2 profile */);
 void         ckh_balancer_destroy(ckh_balancer b);
 /* One Cores.compute-style step: on the first call (all ranges 0) does the equal split + bench=10 pass; later calls use
  * `benchmarkMs`.  `ranges` (in/out, `devices` ints) sums to totalRange afterwards. */

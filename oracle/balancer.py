@@ -88,6 +88,55 @@ def load_balance(benchmark, smooth, history, total_range, global_ranges, step):
     return thr
 
 
+def load_balance_profile(benchmark, total_range, global_ranges, step, last_imbalance=0.0):
+    """Independent restatement of the product's Profile mode (cekirdekler_b200/csrc/host/balance.cpp, profileBalance):
+    no reference counterpart.  Device times are read as a piecewise-constant cost density over the range; the new
+    boundaries cut its integral into equal parts; the move is damped.  In place on `global_ranges`; returns the imbalance
+    (max/mean time of the active devices) the caller passes back as `last_imbalance` on the next call."""
+    n = len(global_ranges)
+    length, dens, total, mx = [], [], 0.0, 0.0
+    for i in range(n):
+        if global_ranges[i] > 0:
+            t = benchmark[i] + 0.01
+            length.append(float(global_ranges[i]))
+            dens.append(t / float(global_ranges[i]))
+            total += t
+            mx = max(mx, t)
+    if not length:
+        return last_imbalance
+    imbalance = mx * float(len(length)) / total
+    target = total / float(n)
+    want, seg, used, assigned = [0.0] * n, 0, 0.0, 0.0
+    for d in range(n - 1):
+        need, got = target, 0.0
+        while seg < len(length):
+            avail = (length[seg] - used) * dens[seg]
+            if avail >= need - 1e-15:
+                take = need / dens[seg] if dens[seg] > 0.0 else 0.0
+                used += take
+                got += take
+                break
+            need -= avail
+            got += length[seg] - used
+            seg += 1
+            used = 0.0
+        want[d] = got
+        assigned += got
+    want[n - 1] = float(total_range) - assigned
+    gain = 0.8 if imbalance > 1.05 else 0.3
+    if last_imbalance > 0.0 and imbalance > 1.02 * last_imbalance and imbalance > 1.05:
+        gain = 0.5
+    for i in range(n):
+        tmp = int(float(global_ranges[i]) + gain * (want[i] - float(global_ranges[i])))
+        rem = _rem(tmp, step)
+        global_ranges[i] = max(0, tmp - rem if rem < _idiv(step, 2) else tmp + (step - rem))
+    while sum(global_ranges) > total_range:
+        global_ranges[max_index(global_ranges)] -= step
+    while sum(global_ranges) < total_range:
+        global_ranges[max_index(global_ranges)] += step
+    return imbalance
+
+
 def initial_split(total_range: int, devices: int):
     ranges = [_idiv(total_range, devices)] * devices
     s = sum(ranges)

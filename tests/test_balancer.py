@@ -136,6 +136,59 @@ def test_adaptive_mode_converges_within_ten_calls_with_smoothing():
     assert max(imb_ref[10:14]) > min(imb_ref[6:10])
 
 
+def oracle_profile_trace(cost_per_item, devices, total, local, calls, speeds=None):
+    csum = np.concatenate([[0.0], np.cumsum(cost_per_item)])
+    ranges, times, last, out = [0] * devices, [0.0] * devices, 0.0, []
+    for _ in range(calls):
+        if all(r == 0 for r in ranges):
+            ranges = ob.initial_split(total, devices)
+            bench = [10.0] * devices
+        else:
+            bench = list(times)
+        last = ob.load_balance_profile(bench, total, ranges, local, last)
+        refs = np.concatenate([[0], np.cumsum(ranges)]).astype(int)
+        times = [float(csum[refs[i] + ranges[i]] - csum[refs[i]]) / (speeds[i] if speeds else 1.0) for i in range(devices)]
+        out.append((list(ranges), times))
+    return out
+
+
+def first_stable_call(trace, devices, tol=1.05, hold=3):
+    imb = [max(t) / (sum(t) / devices) for _, t in trace]
+    for k in range(len(imb) - hold):
+        if all(v <= tol for v in imb[k:k + hold + 1]):
+            return k + 1
+    return None
+
+
+@pytest.mark.parametrize("devices", [2, 3, 4, 8])
+def test_profile_mode_matches_its_restatement_and_converges_within_six_calls(devices):
+    """Profile mode (no reference counterpart): cost density over the range, equal-integral boundaries.  On the
+    Mandelbrot row-cost profile it settles in <= 6 calls (the first is the equal split) at every device count; the
+    reference rule needs 7-11 here and re-diverges later (quirk Q14)."""
+    cost = mandel_row_cost()
+    got = simulate(cost, devices, cost.size, 1, 20, True, mode=2)
+    exp = oracle_profile_trace(cost, devices, cost.size, 1, 20)
+    assert [g[0] for g in got] == [e[0] for e in exp]
+    for r, _ in got:
+        assert sum(r) == cost.size and all(x >= 0 for x in r)
+    k = first_stable_call(got, devices)
+    assert k is not None and k <= 6, k
+
+
+def test_profile_mode_copes_with_unequal_devices_where_the_damped_share_rule_does_not():
+    """One device at 0.3x and one at 0.5x among 8 on position-dependent work: the share rule (reference and adaptive
+    modes) attributes cost to devices, the profile rule to positions; only the latter settles here."""
+    cost = mandel_row_cost()
+    devices, speeds = 8, [0.5, 1, 1, 1, 1, 1, 1, 0.3]
+    tr = oracle_profile_trace(cost, devices, cost.size, 1, 25, speeds)
+    k = first_stable_call(tr, devices)
+    assert k is not None and k <= 10, k
+    uniform = np.full(4096, 0.01)
+    tr = oracle_profile_trace(uniform, 2, uniform.size, 1, 25, [1.0, 0.25])
+    assert first_stable_call(tr, 2) <= 8
+    assert abs(tr[-1][0][0] / uniform.size - 0.8) < 0.02       # 4 : 1 split for a 4 : 1 speed ratio
+
+
 def test_first_call_is_equal_split_with_remainder_on_device_zero():
     h = host()
     b = h.ckh_balancer_create(3, 0)

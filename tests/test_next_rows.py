@@ -47,8 +47,8 @@ def test_opencl_c_idioms_run(gpus):
         tile[l] = in[i];
         barrier(CLK_LOCAL_MEM_FENCE);
         float left = tile[(l + get_local_size(0) - 1) % get_local_size(0)];
-        float4 v = make_float4(tile[l], left, 1.0f, 0.0f);
-        v = v * 2.0f + v;
+        float4 v = (float4)((float2)(tile[l], left), 1.0f, 0.0f);
+        v = v * (float4)(2.0f) + v;
         out[i] = helper(dot(v, v)) + (float)(get_group_id(0) % 2);
         atomic_add(&hist[i % 16], 1);
     }"""

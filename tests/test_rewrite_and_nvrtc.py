@@ -39,6 +39,35 @@ def test_rewrite_leaves_comments_strings_and_lookalikes_alone():
     assert rewrite(src) == src
 
 
+def test_rewrite_turns_vector_literals_into_make_calls():
+    assert rewrite("float4 v = (float4)(a, b, c, d);") == "float4 v = make_float4(a, b, c, d);"
+    assert rewrite("x = ( uint2 ) (1, 2) + (int3)(0);") == "x = make_uint2(1, 2) + make_int3(0);"
+    # casts, lookalikes, comments and strings stay as they are
+    for src in ["y = (float4)v;", "y = (float)(a + b);", "y = (float5)(1);", "y = (myfloat4)(1);", "// (float4)(1,2,3,4)",
+                'printf("(float4)(%f)", q);']:
+        assert rewrite(src) == src
+
+
+def test_vector_literals_and_more_built_ins_compile():
+    src = """
+    float3 reflect3(float3 i, float3 n) { return i - 2.0f * dot(n, i) * n; }
+    __kernel void k(__global const float* in, __global float* out, __global uint* bits)
+    {
+        size_t i = get_global_id(0);
+        float4 v = vload4(i, in);
+        float4 w = (float4)(v.x, (float2)(1.0f, 2.0f), 0.5f) * (float4)(2.0f) + (float4)((float3)(v.y), v.w);
+        w = clamp(mix(w, v, 0.25f), 0.0f, 10.0f) / (1.0f + fabs(w));
+        w -= normalize(v) * length(w.x * v);
+        float3 r = reflect3((float3)(w.x, w.y, w.z), normalize(cross((float3)(1.0f, 0.0f, 0.0f), (float3)(v.x, v.y, 1.0f))));
+        int4 q = convert_int4(w) + (int4)(1, 2, 3, 4);
+        vstore4(mad(w, v, (float4)(r, distance(w, v))) + convert_float4(q), i, out);
+        bits[i] = rotate((uint)q.x, 3u) ^ popcount((uint)q.y) ^ mul24(q.z, q.w) ^ (uint)select(1, 2, q.x > 0);
+        out[4 * i] += smoothstep(0.0f, 1.0f, fract(v.x)) + step(0.5f, v.y) + radians(degrees(v.z));
+    }"""
+    rc, log, _ = compile_check(src)
+    assert rc == 0, log
+
+
 @pytest.mark.parametrize("name", ["stream", "mandelbrot", "nbody", "image"])
 def test_shipped_kernels_build_for_sm_100a(name):
     rc, log, nbytes = compile_check(kernels.source(name))
