@@ -453,8 +453,11 @@ def run_ours(args):
         raise SystemExit("bench.py: no CUDA device visible; there is no CPU fallback (use --impl reference for the CPU arm)")
     pk = peaks()
     spmd_mode = world > 1
+    numa = None
     if spmd_mode:
         spmd.init_process_group_from_env()
+        if os.environ.get("CK_NUMA", "1") != "0":
+            numa = spmd.prefer_host_memory_near_gpu(local)   # pinned arrays on the GPU's own socket
         import torch
         import torch.distributed as dist
 
@@ -638,7 +641,7 @@ def run_ours(args):
                                    f"{E} pixels per work-item, local 256, via ClNumberCruncher.compute",
                        "parallelism": ("spmd one process per GPU" if spmd_mode else "one process") + f" x{n_gpus}",
                        "l2": "output 1 GiB per step >> 126 MB L2, no reuse between steps",
-                       "balancer": args.balancer, "balancer_settle_steps": settle},
+                       "balancer": args.balancer, "balancer_settle_steps": settle, "host_memory_policy_rank0": numa},
             "wall_ms_per_step": wall / args.steps * 1e3,
             "clocks": clk,
             "e2e": {"value": e2e_value, "unit": UNIT, "ms_per_step": e2e_ms, "h2d_bytes_per_step": 32 * n_gpus,

@@ -4,6 +4,7 @@
 
 #include <algorithm>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 
 namespace cekirdekler {
@@ -324,7 +325,55 @@ void Cores::compute(const std::vector<std::string>& kernelNames, int numRepeats,
     };
 
     if (single) {
-        if (ranges[0] > 0) {
+        // One process per GPU: a whole-array `read` input crosses ONE rank's host link (the root rotates) and reaches the
+        // other ranks by ncclBroadcast over NVLink, in place of `world` host uploads.  Every rank takes part, also one
+        // whose share is empty; the ranks agree on the root because they issue the same sequence of calls.
+        // It pays when `world` uploads would queue up on a shared host link: world x bytes / aggregate link rate against one
+        // upload plus ~25 us of NCCL latency.  Measured on 2 B200s a 2 MiB broadcast LOSES 40 us per call to two concurrent
+        // uploads, so the defaults are world >= 4 and arrays >= 512 KiB (CK_SPMD_BROADCAST_MIN_WORLD / _MIN_BYTES override).
+        static const long long minBytes = getenv("CK_SPMD_BROADCAST_MIN_BYTES") ? atoll(getenv("CK_SPMD_BROADCAST_MIN_BYTES")) : (512ll << 10);
+        static const int minWorld = getenv("CK_SPMD_BROADCAST_MIN_WORLD") ? atoi(getenv("CK_SPMD_BROADCAST_MIN_WORLD")) : 4;
+        std::vector<ArrayRef> upArrs = arrs;
+        if (spmdWorld_ > 1 && spmdWorld_ >= minWorld && anyWholeRead && broadcastWholeReads && !noComputeMode &&
+            ckSpmdWorld() == spmdWorld_) {
+            Worker& w = *workers_[0];
+            std::lock_guard<std::mutex> lk(w.mu);
+            ck_handle q = cq ? cq : w.mainQueue();
+            bool timed = false;
+            for (size_t a = 0; a < arrs.size(); a++) {
+                const auto& ar = arrs[a];
+                if (!((ar.flags & F_READ) && !(ar.flags & F_PARTIAL)) || (ar.flags & F_WRITE)) continue;
+                ck_handle b = w.buffer(ar);
+                if (!b || ckBufferIsZeroCopy(b) || ckBufferBytes(b) < minBytes) continue;
+                if (!timed && !enq && ranges[0] > 0) {
+                    bindArgs(0);
+                    w.startBench(deviceClock);
+                    timed = true;
+                }
+                const int root = (int)(spmdBroadcastCalls_++ % (unsigned)spmdWorld_);
+                if (root == spmdRank_) ::writeToBuffer(q, b, ar.host);
+                if (ckSpmdBroadcast(q, b, root) == 0) upArrs[a].flags &= ~(uint32_t)(F_READ | F_PARTIAL);
+            }
+            if (ranges[0] > 0) {
+                if (!timed) {
+                    bindArgs(0);
+                    if (!enq) w.startBench(deviceClock);
+                }
+                w.writeToBuffer(upArrs, refs[0], ranges[0], /*enqueueMode=*/true, cq);
+                launchKernels(0);
+                w.readFromBuffer(arrs, refs[0], ranges[0], base, D, /*enqueueMode=*/true, cq);
+                if (!enq) {
+                    w.stopBench();
+                    finish(w.mainQueue());
+                    w.endBench(computeId);
+                } else {
+                    w.markQueueUsed(w.mainQueue());
+                    if (fineGrainedQueueControl && enqueueModeAsync_) w.addMarker(w.lastUsedQueue() ? w.lastUsedQueue() : w.mainQueue());
+                }
+            } else if (!enq) {
+                finish(q);
+            }
+        } else if (ranges[0] > 0) {
             Worker& w = *workers_[0];
             std::lock_guard<std::mutex> lk(w.mu);
             bindArgs(0);

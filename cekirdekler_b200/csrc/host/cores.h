@@ -108,6 +108,7 @@ class Cores {
     bool enqueueModeAsync_ = false;
     int asyncQueueIndex_ = 0;
     int spmdRank_ = 0, spmdWorld_ = 0;
+    unsigned spmdBroadcastCalls_ = 0;  // rotates the root of rank-to-rank broadcasts; advances identically on every rank
     std::chrono::steady_clock::time_point enqueueT0_;
     std::string ctorError_;
 };

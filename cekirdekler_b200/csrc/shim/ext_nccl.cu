@@ -8,8 +8,11 @@
 // NCCL is loaded at run time (dlopen of libnccl.so.2 — the copy PyTorch already mapped if there is one), so the
 // library keeps loading on machines without NCCL; ckBroadcastUpload then uses its tree of peer copies instead.
 #include "handles.h"
+#include "../../../include/KutuphaneCL.h"
 
 #include <dlfcn.h>
+
+#include <cstring>
 
 #include <map>
 #include <mutex>
@@ -25,6 +28,9 @@ typedef ncclResult_t (*GroupFn)(void);
 typedef ncclResult_t (*BroadcastFn)(const void*, void*, size_t, int, int, ncclComm_t, cudaStream_t);
 typedef ncclResult_t (*CommDestroyFn)(ncclComm_t);
 typedef const char* (*ErrStrFn)(ncclResult_t);
+struct ncclUniqueId { char internal[128]; };   // NCCL_UNIQUE_ID_BYTES
+typedef ncclResult_t (*GetUniqueIdFn)(ncclUniqueId*);
+typedef ncclResult_t (*CommInitRankFn)(ncclComm_t*, int, ncclUniqueId, int);
 
 struct NcclApi {
     void* lib = nullptr;
@@ -33,6 +39,8 @@ struct NcclApi {
     BroadcastFn broadcast = nullptr;
     CommDestroyFn commDestroy = nullptr;
     ErrStrFn errStr = nullptr;
+    GetUniqueIdFn getUniqueId = nullptr;
+    CommInitRankFn commInitRank = nullptr;
     bool ok = false;
 };
 
@@ -52,6 +60,8 @@ static NcclApi& api() {
         x.broadcast = (BroadcastFn)dlsym(x.lib, "ncclBroadcast");
         x.commDestroy = (CommDestroyFn)dlsym(x.lib, "ncclCommDestroy");
         x.errStr = (ErrStrFn)dlsym(x.lib, "ncclGetErrorString");
+        x.getUniqueId = (GetUniqueIdFn)dlsym(x.lib, "ncclGetUniqueId");
+        x.commInitRank = (CommInitRankFn)dlsym(x.lib, "ncclCommInitRank");
         x.ok = x.commInitAll && x.groupStart && x.groupEnd && x.broadcast && x.commDestroy;
         return x;
     }();
@@ -101,4 +111,84 @@ unsigned nccl_next_root(const std::vector<int>& ordinals) {
     return g_root[ordinals]++ % (unsigned)ordinals.size();
 }
 
+// ---- one process per GPU: a communicator over the ranks of the job (ncclCommInitRank), for the same broadcast ----
+static ncclComm_t g_rank_comm = nullptr;
+static int g_rank = -1, g_world = 0;
+
 }  // namespace ck
+
+extern "C" {
+
+// Rank 0 makes the 128-byte id and hands it to the other ranks by whatever channel the job has (torch.distributed here).
+int32_t ckSpmdUniqueId(void* out128) {
+    ck::NcclApi& a = ck::api();
+    if (!a.ok || !a.getUniqueId || !a.commInitRank || !out128) {
+        ck::set_error("ckSpmdUniqueId: NCCL is not available");
+        return -1;
+    }
+    ck::ncclUniqueId id;
+    const ck::ncclResult_t r = a.getUniqueId(&id);
+    if (r != 0) {
+        ck::set_error(std::string("ncclGetUniqueId: ") + (a.errStr ? a.errStr(r) : "error"));
+        return 1;
+    }
+    memcpy(out128, id.internal, sizeof id.internal);
+    return 0;
+}
+
+// Collective over all ranks of the job; `deviceOrdinal` is this rank's GPU.
+int32_t ckSpmdInit(const void* id128, int32_t rank, int32_t world, int32_t deviceOrdinal) {
+    ck::NcclApi& a = ck::api();
+    if (!a.ok || !a.commInitRank || !id128 || world < 1 || rank < 0 || rank >= world) {
+        ck::set_error("ckSpmdInit: NCCL is not available or bad arguments");
+        return -1;
+    }
+    std::lock_guard<std::mutex> lk(ck::g_nccl_mu);
+    if (ck::g_rank_comm) return (ck::g_rank == rank && ck::g_world == world) ? 0 : 2;
+    if (!ck::cuda_ok(cudaSetDevice(deviceOrdinal), "ckSpmdInit: cudaSetDevice")) return 3;
+    ck::ncclUniqueId id;
+    memcpy(id.internal, id128, sizeof id.internal);
+    const ck::ncclResult_t r = a.commInitRank(&ck::g_rank_comm, world, id, rank);
+    if (r != 0) {
+        ck::g_rank_comm = nullptr;
+        ck::set_error(std::string("ncclCommInitRank: ") + (a.errStr ? a.errStr(r) : "error"));
+        return 1;
+    }
+    ck::g_rank = rank;
+    ck::g_world = world;
+    return 0;
+}
+
+int32_t ckSpmdWorld(void) { return ck::g_rank_comm ? ck::g_world : 0; }
+
+// In-place broadcast of the whole buffer from rank `root`, ordered on this rank's queue (every rank calls it).
+int32_t ckSpmdBroadcast(ck_handle hQueue, ck_handle hBuffer, int32_t root) {
+    ck::NcclApi& a = ck::api();
+    if (!ck::g_rank_comm || !hQueue || !hBuffer || root < 0 || root >= ck::g_world) {
+        ck::set_error("ckSpmdBroadcast: no communicator (ckSpmdInit) or bad arguments");
+        return -1;
+    }
+    ck::Queue* q = ck::as<ck::Queue>(hQueue);
+    ck::Buffer* b = ck::as<ck::Buffer>(hBuffer);
+    if (b->zero_copy) {
+        ck::set_error("ckSpmdBroadcast: zero-copy buffers alias host memory and are not broadcast");
+        return -2;
+    }
+    cudaSetDevice(q->ordinal);
+    const ck::ncclResult_t r = a.broadcast(b->dptr, b->dptr, (size_t)b->bytes(), /*ncclChar*/ 0, root, ck::g_rank_comm, q->stream);
+    if (r != 0) {
+        ck::set_error(std::string("ncclBroadcast: ") + (a.errStr ? a.errStr(r) : "error"));
+        return 1;
+    }
+    return 0;
+}
+
+void ckSpmdFinalize(void) {
+    std::lock_guard<std::mutex> lk(ck::g_nccl_mu);
+    if (ck::g_rank_comm && ck::api().commDestroy) ck::api().commDestroy(ck::g_rank_comm);
+    ck::g_rank_comm = nullptr;
+    ck::g_rank = -1;
+    ck::g_world = 0;
+}
+
+}  // extern "C"

@@ -128,12 +128,19 @@ extern "C" int32_t ckNBody3DStepNoAlloc(int32_t device, void* stream, const void
         cudaStream_t s = static_cast<cudaStream_t>(stream);
         const int groups = (bodies + NBW_GROUP - 1) / NBW_GROUP;
         const int counters = NBW_HDR + groups;
+        // The runtime keeps the last error of ANY earlier call on this thread until somebody reads it (a library probing for
+        // optional driver entry points leaves cudaErrorSymbolNotFound behind, seen on an 8-GPU box after NCCL start-up):
+        // drop that first, so that what is read after each launch below belongs to the launch.
+        (void)cudaGetLastError();
         ckna_prepare<<<(counters + 255) / 256, 256, 0, s>>>(base, dt, eps2, n, counters);
-        const unsigned int grid = (unsigned int)(bodies / (CKNA_LOCAL / CKNA_WORK_ITEMS_PER_BODY));
-        ckna_nBody3Dw<<<grid, CKNA_LOCAL, 0, s>>>((unsigned int)firstBody * CKNA_WORK_ITEMS_PER_BODY,
-                                                   static_cast<const float4*>(pos), static_cast<float4*>(vel),
-                                                   static_cast<float4*>(posOut), base, base + CKNA_PARAM_FLOATS);
-        if (!ck::cuda_ok(cudaGetLastError(), "ckNBody3DStepNoAlloc: launch")) rc = 3;
+        if (!ck::cuda_ok(cudaGetLastError(), "ckNBody3DStepNoAlloc: launch of the prepare kernel")) rc = 3;
+        if (rc == 0) {
+            const unsigned int grid = (unsigned int)(bodies / (CKNA_LOCAL / CKNA_WORK_ITEMS_PER_BODY));
+            ckna_nBody3Dw<<<grid, CKNA_LOCAL, 0, s>>>((unsigned int)firstBody * CKNA_WORK_ITEMS_PER_BODY,
+                                                       static_cast<const float4*>(pos), static_cast<float4*>(vel),
+                                                       static_cast<float4*>(posOut), base, base + CKNA_PARAM_FLOATS);
+            if (!ck::cuda_ok(cudaGetLastError(), "ckNBody3DStepNoAlloc: launch of nBody3Dw")) rc = 3;
+        }
     }
     if (previous >= 0 && previous != device) cudaSetDevice(previous);
     return rc;

@@ -50,8 +50,93 @@ def make_exchange(rank: int, world: int, device=None) -> Callable[[List[float]],
     return exchange
 
 
+_broadcast_state = {"tried": False, "ok": False}
+
+
+def init_rank_broadcast(rank: int, world: int, device_ordinal: int, device=None) -> bool:
+    """Collective, once per process: builds the shim's NCCL communicator over the ranks (ckSpmdInit), which lets
+    Cores.compute send a whole-array `read` input over ONE rank's host link and fan it out over NVLink
+    instead of uploading it on every rank.  Rank 0 draws the NCCL id; torch.distributed carries its 128 bytes to the other
+    ranks.  Returns whether every rank has the communicator; without NCCL or GPUs (gloo tests) it returns False and the
+    ranks keep uploading for themselves.  CK_SPMD_BROADCAST=0 switches it off."""
+    import ctypes
+
+    import torch
+    import torch.distributed as dist
+
+    from ._native import shim
+
+    st = _broadcast_state
+    if st["tried"] or world <= 1 or not dist.is_initialized():
+        return st["ok"]
+    st["tried"] = True
+    if os.environ.get("CK_SPMD_BROADCAST", "1") == "0" or os.environ.get("CK_BROADCAST") == "p2p":
+        return False
+    L = shim()
+    buf = (ctypes.c_ubyte * 128)()
+    have = 1
+    if rank == 0:
+        have = 1 if (L.ckDeviceCount() > 0 and L.ckSpmdUniqueId(buf) == 0) else 0
+    t = torch.tensor([have] + list(buf), dtype=torch.int32, device=device)
+    dist.broadcast(t, src=0)
+    vals = t.cpu().tolist()
+    ok = 0
+    if vals[0] == 1 and L.ckDeviceCount() > 0:
+        ident = (ctypes.c_ubyte * 128)(*vals[1:])
+        ok = 1 if L.ckSpmdInit(ident, rank, world, device_ordinal) == 0 else 0
+    elif vals[0] == 1:
+        ok = 0
+    # every rank must have joined, or nobody uses it
+    if vals[0] == 1:
+        flag = torch.tensor([ok], dtype=torch.int32, device=device)
+        dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+        ok = int(flag.item())
+        if not ok:
+            L.ckSpmdFinalize()
+    st["ok"] = bool(ok)
+    return st["ok"]
+
+
 def attach(cruncher, rank: int, world: int, device=None):
     """Put `cruncher` (one device) into SPMD mode as global device `rank` of `world`."""
     if world > 1:
         cruncher.setSpmd(rank, world, make_exchange(rank, world, device))
+        if device is not None and getattr(device, "type", "cpu") == "cuda":
+            init_rank_broadcast(rank, world, cruncher.deviceOrdinals[0] if hasattr(cruncher, "deviceOrdinals") else device.index, device)
     return cruncher
+
+
+def prefer_host_memory_near_gpu(local_rank: int) -> dict:
+    """Make this process allocate its host memory (the pinned arrays above all) on the NUMA node the GPU hangs off.
+
+    With one process per GPU every rank streams its slice over its own host link; when the pinned pages sit on the other
+    socket each transfer also crosses the inter-socket link, which the ranks then share.  Looks the GPU's PCI address up
+    through NVML, reads its node from sysfs and sets the task's memory policy to MPOL_PREFERRED for that node
+    (set_mempolicy(2); threads stay free to run anywhere, so the CPU baseline still gets every core).  Call it before the
+    arrays are created.  Returns what it did; never raises (single-node hosts and containers without sysfs are fine)."""
+    info = {"numa_node": None, "applied": False}
+    try:
+        import ctypes
+        import pynvml
+
+        pynvml.nvmlInit()
+        bus = pynvml.nvmlDeviceGetPciInfo(pynvml.nvmlDeviceGetHandleByIndex(local_rank)).busId
+        bus = (bus.decode() if isinstance(bus, bytes) else bus).lower()
+        if len(bus.split(":")[0]) == 8:
+            bus = bus[4:]                      # NVML prints an 8-digit domain, sysfs a 4-digit one
+        with open(f"/sys/bus/pci/devices/{bus}/numa_node") as f:
+            node = int(f.read().strip())
+        info["numa_node"] = node
+        if node < 0 or not os.path.isdir(f"/sys/devices/system/node/node{node}"):
+            return info
+        MPOL_PREFERRED, SYS_set_mempolicy = 1, 238          # x86-64
+        mask = (ctypes.c_ulong * 16)()
+        mask[node // 64] = 1 << (node % 64)
+        libc = ctypes.CDLL(None, use_errno=True)
+        rc = libc.syscall(SYS_set_mempolicy, MPOL_PREFERRED, mask, 16 * 64)
+        info["applied"] = rc == 0
+        if rc != 0:
+            info["errno"] = ctypes.get_errno()
+    except Exception as e:  # no NVML, no sysfs, seccomp: leave the default policy
+        info["error"] = f"{type(e).__name__}: {e}"
+    return info

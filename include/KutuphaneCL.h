@@ -203,6 +203,17 @@ int32_t   ckBroadcastUpload(ck_handle* hQueues, ck_handle* hBuffers, int32_t nDe
 /* How many broadcasts went through NCCL and through peer-copy trees since the library was loaded. */
 void      ckBroadcastCounts(uint64_t* viaNccl, uint64_t* viaPeerCopies);
 
+/* The same broadcast when every GPU has its own PROCESS (torchrun): a NCCL communicator over the ranks of the job.
+ * Rank 0 calls ckSpmdUniqueId (128 bytes out) and passes the id to the others through the job's own channel; every rank
+ * then calls ckSpmdInit (collective).  ckSpmdBroadcast sends the whole buffer of rank `root` into the same buffer of every
+ * other rank, in place, ordered on each rank's queue; every rank must call it, with the same root.  All return 0 on
+ * success and a negative value when NCCL cannot be loaded (the caller then uploads per rank as the reference does). */
+int32_t   ckSpmdUniqueId(void* out128);
+int32_t   ckSpmdInit(const void* id128, int32_t rank, int32_t world, int32_t deviceOrdinal);
+int32_t   ckSpmdWorld(void);      /* ranks in the communicator, 0 before ckSpmdInit */
+int32_t   ckSpmdBroadcast(ck_handle hCommandQueue, ck_handle hBuffer, int32_t root);
+void      ckSpmdFinalize(void);
+
 /* One n-body step (the nBody3Dw kernel: a += m d / (|d|^2 + eps2)^1.5 over all n bodies, v += a dt, posOut = p + v dt)
  * for bodies [firstBody, firstBody + bodies), WITHOUT allocating anything.  This one has no counterpart in the reference:
  * there every kernel argument is a buffer made by createBuffer, and making a buffer is a cudaMalloc, which drains every
