@@ -367,7 +367,8 @@ def bench_saxpy(ck, kernels, dev, shim, pk, steps, warmup):
     gbs = 12.0 * n / dt / 1e9
     out["resident"] = {"ms_per_step": dt * 1e3, "GBps": gbs,
                        "roofline": {"bound": "hbm", "achieved": gbs, "peak": pk["hbm_gbs"], "unit": "GB/s", "frac": gbs / pk["hbm_gbs"],
-                                    "traffic": None, "peak_source": pk["source"]}}
+                                    "traffic": ncu_traffic("saxpy"), "algorithmic_bytes": 12.0 * n,
+                                    "peak_source": pk["source"] + " (a 1:1 copy; SAXPY's 2 reads : 1 write moves more)"}}
     for a in (alpha, x, y):
         a.dispose()
     cr.dispose()

@@ -328,10 +328,13 @@ void Cores::compute(const std::vector<std::string>& kernelNames, int numRepeats,
         // One process per GPU: a whole-array `read` input crosses ONE rank's host link (the root rotates) and reaches the
         // other ranks by ncclBroadcast over NVLink, in place of `world` host uploads.  Every rank takes part, also one
         // whose share is empty; the ranks agree on the root because they issue the same sequence of calls.
-        // It pays when `world` uploads would queue up on a shared host link: world x bytes / aggregate link rate against one
-        // upload plus ~25 us of NCCL latency.  Measured on 2 B200s a 2 MiB broadcast LOSES 40 us per call to two concurrent
-        // uploads, so the defaults are world >= 4 and arrays >= 512 KiB (CK_SPMD_BROADCAST_MIN_WORLD / _MIN_BYTES override).
-        static const long long minBytes = getenv("CK_SPMD_BROADCAST_MIN_BYTES") ? atoll(getenv("CK_SPMD_BROADCAST_MIN_BYTES")) : (512ll << 10);
+        // It pays when `world` uploads would queue up on a shared host link for longer than the collective costs: a
+        // broadcast makes every rank wait for the slowest one each call, on top of NCCL's own latency.  Measured (round 1,
+        // 2 MiB of positions per call): on 2 B200s the broadcast loses 40 us per call to two concurrent uploads, on 8 it
+        // loses 160 us (n-body step 1.157 ms against 0.995 ms) although the box's host link is shared (107 GB/s aggregate).
+        // With those numbers the break-even is near 4 MB at 8 ranks; the defaults are world >= 4 and arrays >= 16 MiB
+        // (CK_SPMD_BROADCAST_MIN_WORLD / CK_SPMD_BROADCAST_MIN_BYTES override).  Smaller arrays are uploaded by every rank.
+        static const long long minBytes = getenv("CK_SPMD_BROADCAST_MIN_BYTES") ? atoll(getenv("CK_SPMD_BROADCAST_MIN_BYTES")) : (16ll << 20);
         static const int minWorld = getenv("CK_SPMD_BROADCAST_MIN_WORLD") ? atoi(getenv("CK_SPMD_BROADCAST_MIN_WORLD")) : 4;
         std::vector<ArrayRef> upArrs = arrs;
         if (spmdWorld_ > 1 && spmdWorld_ >= minWorld && anyWholeRead && broadcastWholeReads && !noComputeMode &&

@@ -107,7 +107,7 @@ def test_two_ranks_on_two_gpus(gpus, broadcast):
     for rank in range(2):
         env = dict(os.environ, RANK=str(rank), WORLD_SIZE="2", LOCAL_RANK=str(rank), MASTER_ADDR="127.0.0.1",
                    MASTER_PORT=str(port), CK_ROOT=str(ROOT), CK_SPMD_BROADCAST=broadcast,
-                   CK_SPMD_BROADCAST_MIN_WORLD="2", CK_SPMD_BROADCAST_MIN_BYTES="0")   # defaults: world >= 4, >= 512 KiB
+                   CK_SPMD_BROADCAST_MIN_WORLD="2", CK_SPMD_BROADCAST_MIN_BYTES="0")   # defaults: world >= 4, >= 16 MiB
         procs.append(subprocess.Popen([sys.executable, "-c", WORKER], env=env, stdout=subprocess.PIPE, stderr=subprocess.PIPE, text=True))
     outs = []
     for p in procs:
