@@ -56,7 +56,8 @@ def build_shim(force: bool = False) -> Path:
     inc = _embed_prelude()
     srcs = [CSRC / "shim" / "kutuphanecl.cu", CSRC / "shim" / "program.cpp"]
     extra = sorted((CSRC / "shim").glob("ext_*.cu"))
-    deps = srcs + extra + [inc, CSRC / "shim" / "handles.h", ROOT / "include" / "KutuphaneCL.h", Path(__file__)]
+    deps = srcs + extra + [inc, CSRC / "shim" / "handles.h", ROOT / "include" / "KutuphaneCL.h", Path(__file__),
+                           CSRC / "kernels" / "nbody.cu"]   # ext_noalloc.cu compiles the shipped n-body source statically
     out = LIB / "libKutuphaneCL.so"
     if force or _stale(out, deps):
         _run([NVCC, *GENCODE, "-lineinfo", "-O3", "-std=c++17", "-Xcompiler", "-fPIC,-Wall", "-shared",

@@ -5,6 +5,9 @@
 // that no single host link carries every upload), and NCCL broadcasts it from there to the other devices of the
 // cruncher over NVLink.  One process drives all devices (the reference's execution model), so the communicators come
 // from ncclCommInitAll and one thread issues the per-device calls inside a group.
+// With one process per GPU (torchrun) the same broadcast runs over a communicator of the job's ranks instead
+// (ckSpmdUniqueId / ckSpmdInit / ckSpmdBroadcast at the end of this file): rank 0 draws the id, the launcher's own channel
+// carries it, every rank joins; the host layer then lets the root rank upload and all ranks broadcast in place.
 // NCCL is loaded at run time (dlopen of libnccl.so.2 — the copy PyTorch already mapped if there is one), so the
 // library keeps loading on machines without NCCL; ckBroadcastUpload then uses its tree of peer copies instead.
 #include "handles.h"
