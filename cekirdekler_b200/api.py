@@ -250,6 +250,35 @@ class ClArray:
     def N(self) -> int:
         return self._n
 
+    @N.setter
+    def N(self, value: int):
+        """Resize (ClArray.cs:749-800): a new array of the same kind, the first min(old, new) elements kept, the rest zero."""
+        value = int(value)
+        if not getattr(self, "_handle", None) or value == self._n:
+            return
+        self._replace_storage(value, self.fastArr)
+
+    def _replace_storage(self, n: int, fast: bool):
+        """New backing store of `n` elements (pinned native array if `fast`, a language array otherwise) holding the old
+        values; flags, elements per work-item and alignment carry over.  Device buffers are keyed by the array object in
+        the host layer, so the next compute() simply sees a new array."""
+        old_view, keep_n = self.view, min(self._n, n)
+        flags = [self._get(i) for i in range(9)]
+        fresh = ClArray(n, self.dtype, alignmentBytes=max(flags[_F_ALIGN], 1)) if fast else ClArray(np.zeros(n, self.dtype))
+        fresh.view[:keep_n] = old_view[:keep_n]
+        fresh.view[keep_n:] = 0
+        self.dispose()
+        for name in ("_handle", "_keep", "_registered", "view", "_n"):
+            setattr(self, name, getattr(fresh, name))
+        fresh._handle, fresh._registered = None, None       # ownership moved
+        # read/partial/write/writeAll first, then the exclusive switches (which clear the others), then the scalars
+        for i in (_F_READ, _F_PARTIAL, _F_WRITE, _F_WRITEALL, _F_ZC, _F_ELEMS):
+            self._set(i, flags[i])
+        if flags[_F_RO]:
+            self._set(_F_RO, 1)
+        if flags[_F_WO]:
+            self._set(_F_WO, 1)
+
     def __getitem__(self, i):
         return self.view[i]
 
@@ -269,6 +298,13 @@ class ClArray:
     @property
     def fastArr(self) -> bool:
         return bool(self._h.ckh_array_is_fast(self._handle))
+
+    @fastArr.setter
+    def fastArr(self, value: bool):
+        """Switch between the C++ (pinned native) and the language-array representation, keeping the values
+        (ClArray.cs:889-958; exercised by the reference's *ArrayOperations tests, Tester.cs:7470)."""
+        if getattr(self, "_handle", None) and bool(value) != self.fastArr:
+            self._replace_storage(self._n, bool(value))
 
     # -- flags (ClArray.cs:1742-1888)
     def _get(self, i):

@@ -31,6 +31,37 @@ def test_fast_array_operations(ctor, dtype, fill):
     a.dispose()  # callable multiple times (ClArray.cs:848-850)
 
 
+@pytest.mark.parametrize("ctor,dtype,fill", TYPES)
+def test_switching_representation_and_resizing_keep_values_and_flags(ctor, dtype, fill):
+    """The tail of the reference's *ArrayOperations tests (Tester.cs:7465-7483): `fastArr = false`, then CopyFrom/CopyTo
+    must still round-trip; plus the N setter (ClArray.cs:749-800): shorter keeps a prefix, longer pads with zeros."""
+    a = ctor(1024)
+    a.view[:] = (np.arange(1024) % 100).astype(dtype)
+    a.partialRead, a.read, a.numberOfElementsPerWorkItem = True, False, 4
+    before = a.view.copy()
+    a.fastArr = False
+    assert not a.fastArr and a.Length == 1024 and (a.view == before).all()
+    assert a.partialRead and not a.read and a.write and a.numberOfElementsPerWorkItem == 4
+    src = ((35 * np.arange(1024)) % 251).astype(dtype)
+    dst = np.zeros(1024, dtype)
+    a.CopyFrom(src)
+    a.CopyTo(dst)
+    assert (dst == src).all()
+    a.fastArr = True
+    assert a.fastArr and (a.view == src).all() and a.view.ctypes.data % 4096 == 0
+    a.N = 300
+    assert a.N == 300 and a.Length == 300 and a.fastArr and (a.view == src[:300]).all()
+    a.N = 2000
+    assert a.N == 2000 and (a.view[:300] == src[:300]).all() and not a.view[300:].any()
+    assert a.partialRead and a.numberOfElementsPerWorkItem == 4
+    ro = ctor(64)
+    ro.readOnly = True
+    ro.fastArr = False
+    assert ro.readOnly and not ro.write and not ro.fastArr
+    a.dispose()
+    ro.dispose()
+
+
 def test_alignment_parameter():
     a = ck.ClArray(100, np.float32, alignmentBytes=65536)
     assert a.view.ctypes.data % 65536 == 0

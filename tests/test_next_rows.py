@@ -74,3 +74,25 @@ def test_devices_sorted_by_nbody_micro_benchmark(gpus):
     devs = ck.ClPlatforms.all().gpus()
     ranked = devs.devicesWithHighestDirectNbodyPerformance(4096)
     assert sorted(ranked.ordinals) == sorted(devs.ordinals)
+
+
+def test_compute_follows_an_array_that_was_resized_or_switched(gpus):
+    """ClArray.N and ClArray.fastArr replace the backing store (ClArray.cs:749-800, :889-958); the next compute() must
+    use the new one, on every device of the split."""
+    cr = ck.ClNumberCruncher(ck.ClPlatforms.all().gpus(), kernels.reference_copy_kernel("float"))
+    assert cr.errorCode() == 0, cr.errorMessage()
+    n = 256 * 64
+    a, b = ck.ClFloatArray(n), ck.ClFloatArray(n)
+    a.view[:] = np.arange(n)
+    assert a.nextParam(b).compute(cr, 1, "test", n, 256) == 0
+    assert np.array_equal(b.view, a.view)
+    for arr in (a, b):
+        arr.N = 2 * n
+    a.view[n:] = -np.arange(n)
+    a.fastArr = False
+    assert a.nextParam(b).compute(cr, 1, "test", 2 * n, 256) == 0
+    assert np.array_equal(b.view, a.view) and b.view[n + 5] == -5
+    b.fastArr = False
+    b.view[:] = 0
+    assert a.nextParam(b).compute(cr, 1, "test", 2 * n, 256) == 0
+    assert np.array_equal(b.view, a.view)
