@@ -508,6 +508,13 @@ class ClNumberCruncher:
     def lastComputePerformanceReport(self, computeId: int = 0) -> str:
         return self._h.ckh_cruncher_performance_report(self._handle, computeId).decode()
 
+    def performanceHistory(self, computeId: int) -> List[List[float]]:
+        """Cores.performanceHistory (Cores.cs:1075-1098): the balancer's 10-deep window of normalised throughput shares,
+        oldest row first, one column per device; all zero before the compute id has run."""
+        buf = (C.c_double * (10 * 64))()
+        d = self._h.ckh_cruncher_performance_history(self._handle, computeId, buf, len(buf))
+        return [[buf[k * d + j] for j in range(d)] for k in range(10)] if d else []
+
     def _ivec(self, fn, computeId) -> List[int]:
         buf = (C.c_int32 * 64)()
         n = fn(self._handle, computeId, buf, 64)

@@ -180,6 +180,20 @@ const char* ckh_cruncher_performance_report(ckh_cruncher c, int32_t id) {
     if (!c || !CR(c).numberCruncher()) return keep("Error: Number cruncher core object was not allocated properly.");
     return keep(CR(c).numberCruncher()->performanceReport(id));
 }
+int32_t ckh_cruncher_performance_history(ckh_cruncher c, int32_t id, double* out, int32_t cap) {
+    // Cores.performanceHistory (Cores.cs:1075-1098): kHistoryDepth rows of normalised throughput shares, oldest first;
+    // all zero for a compute id that has not run (the reference creates the zero matrix on first access)
+    if (!c || !CR(c).numberCruncher() || !out) return 0;
+    auto* cores = CR(c).numberCruncher();
+    auto* st = cores->state(id);
+    const int devices = st && !st->balance.history.empty() ? (int)st->balance.history[0].size()
+                                                            : (cores->spmdWorld() > 0 ? cores->spmdWorld() : cores->numberOfDevices());
+    if (cap < kHistoryDepth * devices) return 0;
+    for (int k = 0; k < kHistoryDepth; k++)
+        for (int j = 0; j < devices; j++)
+            out[k * devices + j] = (st && (int)st->balance.history.size() == kHistoryDepth) ? st->balance.history[k][j] : 0.0;
+    return devices;
+}
 int32_t ckh_cruncher_ranges(ckh_cruncher c, int32_t id, int32_t* out, int32_t n) {
     if (!c || !CR(c).numberCruncher()) return 0;
     auto* st = CR(c).numberCruncher()->state(id);

@@ -62,6 +62,9 @@ int32_t     ckh_cruncher_markers_reached(ckh_cruncher c);            /* :367-372
 void        ckh_cruncher_flush_last_used_queue(ckh_cruncher c);      /* :141-145 */
 void        ckh_cruncher_sync(ckh_cruncher c);
 const char* ckh_cruncher_performance_report(ckh_cruncher c, int32_t computeId);   /* Cores.cs:994-1063 */
+/* Cores.performanceHistory (Cores.cs:1075-1098): 10 rows x devices normalised shares, oldest row first, row-major into
+ * `out` (capacity in doubles); returns the number of devices, 0 if `out` is too small */
+int32_t     ckh_cruncher_performance_history(ckh_cruncher c, int32_t computeId, double* out, int32_t capacity);
 /* fill `out` (capacity n) and return the number of devices the range is split over                  */
 int32_t     ckh_cruncher_ranges(ckh_cruncher c, int32_t computeId, int32_t* out, int32_t n);            /* Cores.globalRanges */
 int32_t     ckh_cruncher_references(ckh_cruncher c, int32_t computeId, int32_t* out, int32_t n);        /* Cores.globalReferences */

@@ -140,6 +140,9 @@ def test_performance_report_and_normalised_shares(gpus):
     powers = cr.normalizedComputePowersOfDevices()
     assert abs(sum(powers) - 1.0) < 1e-9
     assert len(cr.deviceNames()) == gpus and all("NVIDIA" in n for n in cr.deviceNames())
+    hist = cr.performanceHistory(5)                  # Cores.cs:1075-1098: 10 rows, newest last, one column per device
+    assert len(hist) == 10 and all(len(r) == gpus for r in hist)
+    assert abs(sum(hist[-1]) - 1.0) < 1e-9 and not any(cr.performanceHistory(77)[0])
 
 
 def test_whole_read_inputs_are_broadcast_over_nvlink(gpus):
