@@ -16,7 +16,7 @@
 // Roofline: 4 FMA-pipe operations per iteration (FFMA, FMUL, FFMA-with-immediate, FFMA), none of which reads more than
 // two distinct registers.  That matters on Blackwell: an instruction that needs two source registers from the same
 // (even/odd) register bank issues over two cycles, and the textbook y' = fma(x+x, y, cy) — three distinct registers —
-// always does.  Measured on B200 with all lanes in the set (build/exp micro-benchmark, round 1): textbook 5-op form
+// always does.  Measured on B200 with all lanes in the set (profiles/experiments micro-benchmark, round 1): textbook 5-op form
 // 6.35 issue slots per iteration (63 % of the FP32 peak in 8-FLOP units), this form 4.29 slots (93 %) with blocks of 32.
 // The escape test is hoisted out of the inner loop: a block of iterations runs unchecked, then one test; if the orbit left
 // the radius-2 disc inside the block, the block is replayed from its saved start with a per-iteration test to find the
@@ -30,7 +30,7 @@
 #define MANDEL_K1 8    // short unchecked blocks first: most pixels outside the set leave within a few iterations, and a
 #define MANDEL_B1 4    // short block keeps both the wasted unchecked work and the replay small for them ...
 #define MANDEL_K2 64   // ... then long blocks, where the per-block test/bookkeeping is 12 instructions per 256 useful ones
-// Measured on the full 16384^2 x 4096 image on B200 (build/exp/mv.cu, round 1): one block length of 32 -> 25.31 ms (78.8 % of
+// Measured on the full 16384^2 x 4096 image on B200 (profiles/experiments/mv.cu, round 1): one block length of 32 -> 25.31 ms (78.8 % of
 // the FP32 peak), 64 -> 25.03 ms, 4 blocks of 8 then blocks of 64 -> 24.04 ms (83.0 %); identical iteration counts.
 
 // exact per-iteration loop: at most `limit` iterations from state (x, y); returns the number executed before escape
