@@ -434,6 +434,28 @@ def bench_nbody(ck, kernels, po, devs, pk, sms, steps, warmup, spmd_attach=None,
                         "traffic": ncu_traffic("nbody") if n_gpus == 1 else None,
                         "note": "20 FLOP per interaction over the kernel's own launch time (arrays resident); GInter_per_s "
                                 "adds the 2 MiB position upload and the slice transfers, GInter_per_s_e2e the whole host call"}}
+    if n_gpus > 1 and spmd_attach is None:
+        # One process driving all devices: correct device-resident stepping with the exchange fused into the kernel
+        # (nBody3Dwp: every device stores its new positions and velocities into all devices' buffers over NVLink).
+        # Positions go up once; after that a step is the kernel and nothing else.
+        t_a, t_b = cr.peerTable(pa, vel), cr.peerTable(pb, vel)
+        pa.view[:] = pos.reshape(-1)
+        params.readOnly = True
+        src, dst, ts_p, ts_pw = pa, pb, [], []
+        for i in range(3 + steps):
+            src.read, src.partialRead, src.write = (i == 0), False, False
+            t0 = time.perf_counter()
+            assert src.nextParam(vel, dst, params, scratch, t_b if dst is pb else t_a).compute(cr, 2, "nBody3Dwp", n * per_body, local) == 0
+            if i >= 3:
+                ts_pw.append(time.perf_counter() - t0)
+                ts_p.append(max(cr.benchmarks(2)) * 1e-3)
+            src, dst = dst, src
+        dt_p, dt_pw = float(np.mean(ts_p)), float(np.mean(ts_pw))
+        res["resident_peer_stores"] = {"kernel": "nBody3Dwp", "ms_per_step_device": dt_p * 1e3, "ms_per_step_e2e": dt_pw * 1e3,
+                                       "GInter_per_s": inter / dt_p / 1e9, "GInter_per_s_e2e": inter / dt_pw / 1e9,
+                                       "frac_of_fp32_per_gpu": 20.0 * inter / n_gpus / dt_p / 1e12 / peak}
+        for t in (t_a, t_b):
+            t.dispose()
     for a in (pa, pb, vel, params, scratch):
         a.dispose()
     cr.dispose()

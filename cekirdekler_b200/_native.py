@@ -139,6 +139,7 @@ def host() -> C.CDLL:
             "ckh_cruncher_flush_last_used_queue": (None, [vp]), "ckh_cruncher_sync": (None, [vp]),
             "ckh_cruncher_performance_report": (cp, [vp, i32]),
             "ckh_cruncher_performance_history": (i32, [vp, i32, pdbl, i32]),
+            "ckh_cruncher_buffer_pointer": (u64, [vp, vp, i32]),
             "ckh_cruncher_ranges": (i32, [vp, i32, pi32, i32]), "ckh_cruncher_references": (i32, [vp, i32, pi32, i32]),
             "ckh_cruncher_benchmarks": (i32, [vp, i32, pdbl, i32]),
             "ckh_cruncher_normalized_compute_powers": (i32, [vp, pdbl, i32]),

@@ -508,6 +508,24 @@ class ClNumberCruncher:
     def lastComputePerformanceReport(self, computeId: int = 0) -> str:
         return self._h.ckh_cruncher_performance_report(self._handle, computeId).decode()
 
+    def peerTable(self, *targets: "ClArray") -> "ClArray":
+        """(No reference counterpart.)  A small whole-`read` array for kernels that store into the OTHER devices' copies of
+        the target arrays over NVLink (nBody3Dwp): element 0 = D, the number of devices of this cruncher; then, for each
+        target in turn, the device address of its buffer on device 0..D-1.  The buffers are created here if compute() has
+        not made them yet; the table stays valid until a target is resized or disposed.  One process driving all devices
+        only: in one-process-per-GPU mode the other buffers live in other address spaces."""
+        n = self.numberOfDevices
+        table = ClArray(1 + max(n, 1) * max(len(targets), 1), np.int64)
+        table.view[0] = n
+        for t, target in enumerate(targets):
+            for i in range(n):
+                p = self._h.ckh_cruncher_buffer_pointer(self._handle, target._handle, i)
+                if not p:
+                    raise RuntimeError("peerTable: no device buffer for target %d on device %d" % (t, i))
+                table.view[1 + t * n + i] = np.array([p], dtype=np.uint64).view(np.int64)[0]
+        table.readOnly = True
+        return table
+
     def performanceHistory(self, computeId: int) -> List[List[float]]:
         """Cores.performanceHistory (Cores.cs:1075-1098): the balancer's 10-deep window of normalised throughput shares,
         oldest row first, one column per device; all zero before the compute id has run."""

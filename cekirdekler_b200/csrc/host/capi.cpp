@@ -180,6 +180,18 @@ const char* ckh_cruncher_performance_report(ckh_cruncher c, int32_t id) {
     if (!c || !CR(c).numberCruncher()) return keep("Error: Number cruncher core object was not allocated properly.");
     return keep(CR(c).numberCruncher()->performanceReport(id));
 }
+uint64_t ckh_cruncher_buffer_pointer(ckh_cruncher c, ckh_array a, int32_t deviceIndex) {
+    // device address of the buffer that device `deviceIndex` of the cruncher keeps for `a` (created on first use, as
+    // compute() would); 0 on error.  Feeds the peer tables of kernels that store into other devices' buffers.
+    if (!c || !a || !CR(c).numberCruncher()) return 0;
+    Cores* cores = CR(c).numberCruncher();
+    if (deviceIndex < 0 || deviceIndex >= cores->numberOfDevices()) return 0;
+    Worker& w = cores->worker(deviceIndex);
+    std::lock_guard<std::mutex> lk(w.mu);
+    ck_handle b = w.buffer(static_cast<ClArray*>(a)->ref());
+    if (!b || ckBufferIsZeroCopy(b)) return 0;
+    return (uint64_t)(uintptr_t)ckBufferDevicePointer(b);
+}
 int32_t ckh_cruncher_performance_history(ckh_cruncher c, int32_t id, double* out, int32_t cap) {
     // Cores.performanceHistory (Cores.cs:1075-1098): kHistoryDepth rows of normalised throughput shares, oldest first;
     // all zero for a compute id that has not run (the reference creates the zero matrix on first access)

@@ -336,8 +336,13 @@ __kernel void nBody3Dq(const float4* __restrict__ pos, float4* __restrict__ vel,
 #define NBW_HDR 4                // ints before the per-group counters
 #define NBW_TILES_PER_WARP 2     // j tiles a warp sweeps per unit
 
-__kernel void nBody3Dw(const float4* __restrict__ pos, float4* __restrict__ vel, float4* __restrict__ posOut,
-                       const float* __restrict__ params, float* __restrict__ scratch)
+// The step itself, shared by nBody3Dw and nBody3Dwp (below).  With NBW_PEERS the integrating work-group also stores each
+// new position into the posOut buffers of the other devices (peers[0] = count, peers[1..] = device pointers, NVLink peer
+// stores), so that after the launch EVERY device holds the complete new positions and the next step needs no host.
+template <bool NBW_PEERS>
+__device__ __forceinline__ void ck_nbw_step(const unsigned int __ck_goff, const float4* __restrict__ pos, float4* __restrict__ vel,
+                                            float4* __restrict__ posOut, const float* __restrict__ params,
+                                            float* __restrict__ scratch, const unsigned long long* __restrict__ peers)
 {
     __shared__ float4 sA[NBW_MAXW][NB_TILE / 2];
     __shared__ float4 sB[NBW_MAXW][NB_TILE / 2];
@@ -510,7 +515,21 @@ __kernel void nBody3Dw(const float4* __restrict__ pos, float4* __restrict__ vel,
                     v.y = __fmaf_rn(ay, dt, v.y);
                     v.z = __fmaf_rn(az, dt, v.z);
                     vel[body] = v;
-                    posOut[body] = make_float4(__fmaf_rn(v.x, dt, p.x), __fmaf_rn(v.y, dt, p.y), __fmaf_rn(v.z, dt, p.z), p.w);
+                    const float4 np = make_float4(__fmaf_rn(v.x, dt, p.x), __fmaf_rn(v.y, dt, p.y), __fmaf_rn(v.z, dt, p.z), p.w);
+                    posOut[body] = np;
+                    if (NBW_PEERS) {
+                        // 16-byte stores over NVLink, two per body and peer: the position for the next step, and the velocity
+                        // so that the body can change owner when the balancer moves the split
+                        const int count = (int)peers[0];
+                        for (int d = 1; d <= count; d++) {
+                            float4* remotePos = reinterpret_cast<float4*>(peers[d]);
+                            float4* remoteVel = reinterpret_cast<float4*>(peers[count + d]);
+                            if (remotePos != posOut) {
+                                remotePos[body] = np;
+                                remoteVel[body] = v;
+                            }
+                        }
+                    }
                 }
             }
             if (threadIdx.x == 0) done[g] = 0;
@@ -529,4 +548,24 @@ __kernel void nBody3Dw(const float4* __restrict__ pos, float4* __restrict__ vel,
             ctr[1] = 0;
         }
     }
+}
+
+__kernel void nBody3Dw(const float4* __restrict__ pos, float4* __restrict__ vel, float4* __restrict__ posOut,
+                       const float* __restrict__ params, float* __restrict__ scratch)
+{
+    ck_nbw_step<false>((unsigned int)get_global_offset(0), pos, vel, posOut, params, scratch, nullptr);
+}
+
+// nBody3Dwp — the step fused with the exchange that follows it when the bodies are split over several devices and stay
+// there: compute (range split) + all-gather of the new positions in ONE kernel, over peer memory.  In the reference's model
+// every step round-trips through the host (download the slices, upload the whole array to every device: Worker.cs:833-834);
+// with `peers` = { D, posOut on device 0..D-1, vel on device 0..D-1 } (device addresses; ClNumberCruncher.peerTable(posOut,
+// vel) in api.py fills it) the integrating work-groups write each new position and velocity to every device, and the next
+// step runs with read/write flags off.  Every device then holds complete arrays, so the balancer may move the split freely.
+// The host-side finish of all devices at the end of compute() is the only synchronisation needed between steps.
+__kernel void nBody3Dwp(const float4* __restrict__ pos, float4* __restrict__ vel, float4* __restrict__ posOut,
+                        const float* __restrict__ params, float* __restrict__ scratch,
+                        const unsigned long long* __restrict__ peers)
+{
+    ck_nbw_step<true>((unsigned int)get_global_offset(0), pos, vel, posOut, params, scratch, peers);
 }

@@ -41,8 +41,10 @@
 #define nBody3D(...) ckna_nBody3D(const unsigned int __ck_goff, __VA_ARGS__)
 #define nBody3Dq(...) ckna_nBody3Dq(const unsigned int __ck_goff, __VA_ARGS__)
 #define nBody3Dw(...) ckna_nBody3Dw(const unsigned int __ck_goff, __VA_ARGS__)
+#define nBody3Dwp(...) ckna_nBody3Dwp(const unsigned int __ck_goff, __VA_ARGS__)
 #pragma nv_diag_suppress 177   // the file's other kernels come along unused
 #include "../kernels/nbody.cu"
+#undef nBody3Dwp
 #undef nBody2D
 #undef nBody3D1
 #undef nBody3D

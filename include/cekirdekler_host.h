@@ -62,6 +62,10 @@ int32_t     ckh_cruncher_markers_reached(ckh_cruncher c);            /* :367-372
 void        ckh_cruncher_flush_last_used_queue(ckh_cruncher c);      /* :141-145 */
 void        ckh_cruncher_sync(ckh_cruncher c);
 const char* ckh_cruncher_performance_report(ckh_cruncher c, int32_t computeId);   /* Cores.cs:994-1063 */
+/* Device address of the buffer that device `deviceIndex` of the cruncher keeps for array `a` (created on first use, like
+ * compute() does; 0 on error or for zero-copy arrays).  No reference counterpart: it feeds the peer-pointer tables of
+ * kernels that write into the other devices' buffers over NVLink (nBody3Dwp). */
+uint64_t    ckh_cruncher_buffer_pointer(ckh_cruncher c, ckh_array a, int32_t deviceIndex);
 /* Cores.performanceHistory (Cores.cs:1075-1098): 10 rows x devices normalised shares, oldest row first, row-major into
  * `out` (capacity in doubles); returns the number of devices, 0 if `out` is too small */
 int32_t     ckh_cruncher_performance_history(ckh_cruncher c, int32_t computeId, double* out, int32_t capacity);

@@ -340,6 +340,50 @@ def test_nbody3d_work_queue_is_split_independent_and_fits_small_scratch(gpus):
     assert not refused.any()                                                    # untouched output, message on the device's stdout
 
 
+def test_nbody3d_resident_steps_with_peer_stores(gpus):
+    """nBody3Dwp: the step fused with the exchange of its results.  Positions are uploaded once; after that every device
+    writes its share of new positions and velocities into ALL devices' buffers (NVLink peer stores), so the following steps
+    move nothing over the host link, and only the last one downloads.  Must match the oracle like the host-mediated path,
+    on one device (no peers to write to) as on several, and while the balancer moves the split."""
+    n, steps, wpb, local = 16384, 6, 4, 128
+    pos0 = nbody3d_inputs(n)
+    params_h = np.array([1e-3, 1e-4, n, 0], np.float32)
+    p, v, o = pos0.copy().reshape(-1), np.zeros(4 * n, np.float32), np.zeros(4 * n, np.float32)
+    for _ in range(steps):
+        po.nbody3d_step(p, v, o, params_h)
+        p, o = o, p
+    cr = ck.ClNumberCruncher(all_gpus(), kernels.source("nbody"))
+    assert cr.errorCode() == 0, cr.errorMessage()
+    kfloats = ((n // 128 + 8) * ((n // 256 + 7) // 8) * 384 + 4096) // 1024
+    pa, pb, vel, params, scratch = (ck.ClFloatArray(4 * n), ck.ClFloatArray(4 * n), ck.ClFloatArray(4 * n), ck.ClFloatArray(8),
+                                    ck.ClFloatArray(kfloats * 1024))
+    pa.view[:] = pos0.reshape(-1)
+    params.view[:5] = [1e-3, 1e-4, n, wpb, kfloats]
+    params.readOnly = True
+    scratch.read, scratch.write = False, False
+    for a in (pa, pb, vel):
+        a.numberOfElementsPerWorkItem = 4 // wpb
+    tables = {id(pa): cr.peerTable(pa, vel), id(pb): cr.peerTable(pb, vel)}
+    assert tables[id(pa)].view[0] == gpus and len(set(tables[id(pa)].view[1:1 + gpus].tolist())) == gpus
+    src, dst = pa, pb
+    for s in range(steps):
+        last = s == steps - 1
+        src.read, src.partialRead, src.write = (s == 0), False, False        # the only upload of positions
+        dst.read, dst.partialRead, dst.write = False, False, last            # the only download
+        vel.read, vel.partialRead, vel.write = False, False, last            # starts at zero in the (zero-filled) buffers
+        host_before = dst.view.copy()
+        assert src.nextParam(vel, dst, params, scratch, tables[id(dst)]).compute(cr, 1, "nBody3Dwp", n * wpb, local) == 0
+        if not last:
+            assert np.array_equal(dst.view, host_before) and not vel.view.any()   # nothing came back to the host in between
+        src, dst = dst, src
+    got, exp = src.view.reshape(n, 4), p.reshape(n, 4)
+    rel = np.abs(got[:, :3] - exp[:, :3]) / np.maximum(np.abs(exp[:, :3]), 1e-3)
+    assert rel.max() <= 1e-4, rel.max()
+    assert np.array_equal(got[:, 3], exp[:, 3])
+    vexp = v.reshape(n, 4)[:, :3]
+    assert np.abs(vel.view.reshape(n, 4)[:, :3] - vexp).max() / np.abs(vexp).max() <= 1e-4
+
+
 # ------------------------------------------------------------------ blur → Sobel → histogram (K5)
 @pytest.mark.parametrize("W,H", [(256, 128), (3840, 2160)])
 def test_image_chain_bit_exact(gpus, W, H):
