@@ -82,6 +82,7 @@ def shim() -> C.CDLL:
             "ckBroadcastUpload": (i32, [C.POINTER(vp), C.POINTER(vp), i32, vp]),
             "ckBroadcastCounts": (None, [C.POINTER(u64), C.POINTER(u64)]),
             "ckNBody3DStepNoAlloc": (i32, [i32, vp, vp, vp, vp, i32, i32, i32, C.c_float, C.c_float]),
+            "ckIpcExport": (i32, [i32, vp, vp]), "ckIpcOpen": (vp, [i32, vp]), "ckIpcClose": (i32, [i32, vp]),
             "ckSpmdUniqueId": (i32, [vp]), "ckSpmdInit": (i32, [vp, i32, i32, i32]), "ckSpmdWorld": (i32, []),
             "ckSpmdBroadcast": (i32, [vp, vp, i32]), "ckSpmdFinalize": (None, []),
         }

@@ -106,6 +106,75 @@ def attach(cruncher, rank: int, world: int, device=None):
     return cruncher
 
 
+class PeerTable:
+    """The one-process-per-GPU form of ClNumberCruncher.peerTable: `array` is a whole-`read` ClArray holding
+    { world, target0 on rank 0..world-1, target1 on rank 0..world-1, ... } as device addresses valid in THIS process — the
+    own buffers directly, the other ranks' buffers through CUDA IPC (handles all-gathered over torch.distributed).
+    Collective: every rank constructs it with the same targets in the same order, then checks `ok` (the same on every
+    rank; `error` says what failed locally) before using `array`.  close() is collective too (a barrier first, so that
+    nobody unmaps or frees a buffer another rank's kernel may still be writing)."""
+
+    def __init__(self, cruncher, rank: int, world: int, device, *targets):
+        import ctypes
+
+        import numpy as np
+        import torch
+        import torch.distributed as dist
+
+        from ._native import shim
+        from .api import ClArray
+
+        # Nothing below raises between the collectives: a rank that fails keeps taking part and reports through `ok`
+        # (the minimum over ranks), so that either every rank uses the table or none does.
+        self._L, self._dev, self._opened = shim(), device.index, []
+        self.error = ""
+        L, h = self._L, cruncher._h
+        own = []
+        blob = torch.zeros(len(targets) * 64, dtype=torch.uint8)
+        for t, target in enumerate(targets):
+            p = h.ckh_cruncher_buffer_pointer(cruncher._handle, target._handle, 0)
+            own.append(p)
+            raw = (ctypes.c_ubyte * 64)()
+            if not p or L.ckIpcExport(self._dev, ctypes.c_void_p(p), raw) != 0:
+                self.error = self.error or ("export of target %d: %s" % (t, L.ckGetLastError().decode()))
+            blob[t * 64:(t + 1) * 64] = torch.tensor(list(raw), dtype=torch.uint8)
+        gathered = torch.zeros(world * blob.numel(), dtype=torch.uint8, device=device)
+        dist.all_gather_into_tensor(gathered, blob.to(device))
+        handles = gathered.cpu().numpy().reshape(world, len(targets), 64)
+        self.array = ClArray(1 + world * max(len(targets), 1), np.int64)
+        self.array.view[0] = world
+        for t in range(len(targets)):
+            for r in range(world):
+                if r == rank:
+                    p = own[t]
+                elif self.error:
+                    p = 0
+                else:
+                    raw = (ctypes.c_ubyte * 64)(*handles[r, t].tolist())
+                    p = L.ckIpcOpen(self._dev, raw) or 0
+                    if p:
+                        self._opened.append(p)
+                    else:
+                        self.error = "open of rank %d target %d: %s" % (r, t, L.ckGetLastError().decode())
+                self.array.view[1 + t * world + r] = np.array([p], dtype=np.uint64).view(np.int64)[0]
+        self.array.readOnly = True
+        flag = torch.tensor([0 if self.error else 1], dtype=torch.int32, device=device)
+        dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+        self.ok = bool(flag.item())
+
+    def close(self):
+        import torch.distributed as dist
+
+        if dist.is_initialized():
+            dist.barrier()
+        for p in self._opened:
+            self._L.ckIpcClose(self._dev, p)
+        self._opened = []
+        if dist.is_initialized():
+            dist.barrier()                     # owners free their buffers only after every importer has unmapped them
+        self.array.dispose()
+
+
 def prefer_host_memory_near_gpu(local_rank: int) -> dict:
     """Make this process allocate its host memory (the pinned arrays above all) on the NUMA node the GPU hangs off.
 

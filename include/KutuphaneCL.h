@@ -214,6 +214,14 @@ int32_t   ckSpmdWorld(void);      /* ranks in the communicator, 0 before ckSpmdI
 int32_t   ckSpmdBroadcast(ck_handle hCommandQueue, ck_handle hBuffer, int32_t root);
 void      ckSpmdFinalize(void);
 
+/* Device buffers of other processes (one process per GPU), for kernels that store into every GPU's copy of an array over
+ * NVLink: export a 64-byte handle of a cudaMalloc'd buffer of this process, open another process's handle (the returned
+ * device pointer is usable by kernels on `device`), close it again.  The owner keeps the buffer alive until every importer
+ * has closed it.  Export/close return 0 on success; open returns NULL on failure (ckGetLastError has the text). */
+int32_t   ckIpcExport(int32_t device, void* devicePointer, void* out64);
+void*     ckIpcOpen(int32_t device, const void* handle64);
+int32_t   ckIpcClose(int32_t device, void* importedPointer);
+
 /* One n-body step (the nBody3Dw kernel: a += m d / (|d|^2 + eps2)^1.5 over all n bodies, v += a dt, posOut = p + v dt)
  * for bodies [firstBody, firstBody + bodies), WITHOUT allocating anything.  This one has no counterpart in the reference:
  * there every kernel argument is a buffer made by createBuffer, and making a buffer is a cudaMalloc, which drains every
