@@ -375,7 +375,8 @@ def bench_saxpy(ck, kernels, dev, shim, pk, steps, warmup):
     return out
 
 
-def bench_nbody(ck, kernels, po, devs, pk, sms, steps, warmup, spmd_attach=None, n_gpus=1, allmax=lambda v: v, spmd_ctx=None):
+def bench_nbody(ck, kernels, po, devs, pk, sms, steps, warmup, spmd_attach=None, n_gpus=1, allmax=lambda v: v, spmd_ctx=None,
+                defer_finish=False):
     """C4: all-pairs n-body, 128 Ki bodies float4; pos is a whole-array read, vel/posOut are sliced."""
     n = 131072
     cr = ck.ClNumberCruncher(devs, kernels.source("nbody"))
@@ -434,46 +435,54 @@ def bench_nbody(ck, kernels, po, devs, pk, sms, steps, warmup, spmd_attach=None,
                         "traffic": ncu_traffic("nbody") if n_gpus == 1 else None,
                         "note": "20 FLOP per interaction over the kernel's own launch time (arrays resident); GInter_per_s "
                                 "adds the 2 MiB position upload and the slice transfers, GInter_per_s_e2e the whole host call"}}
-    if n_gpus > 1 and (spmd_attach is None or spmd_ctx is not None):
-        # Correct device-resident stepping with the exchange fused into the kernel (nBody3Dwp: every device stores its new
-        # positions and velocities into all devices' buffers over NVLink — directly when one process drives all devices,
-        # through CUDA IPC mappings when each GPU has its own process).  Positions go up once; after that a step is the
-        # kernel and nothing else.  In one-process-per-GPU mode the exchange of device times that opens every compute()
-        # is the barrier between steps.
-        if spmd_ctx is not None:
-            from cekirdekler_b200 import spmd as _spmd
+    def finish():
+        """The device-resident leg (when there is more than one device) and the clean-up.  Deferred on request so that the
+        caller can have the rest of its result line ready before it starts (see the watchdog in run_ours)."""
+        if n_gpus > 1 and (spmd_attach is None or spmd_ctx is not None):
+            # Correct device-resident stepping with the exchange fused into the kernel (nBody3Dwp: every device stores its new
+            # positions and velocities into all devices' buffers over NVLink — directly when one process drives all devices,
+            # through CUDA IPC mappings when each GPU has its own process).  Positions go up once; after that a step is the
+            # kernel and nothing else.  In one-process-per-GPU mode the exchange of device times that opens every compute()
+            # is the barrier between steps.
+            if spmd_ctx is not None:
+                from cekirdekler_b200 import spmd as _spmd
 
-            tabs = [_spmd.PeerTable(cr, spmd_ctx[0], spmd_ctx[1], spmd_ctx[2], x, vel) for x in (pa, pb)]
-            t_a, t_b = tabs[0].array, tabs[1].array
-            usable = all(t.ok for t in tabs)      # the same on every rank
-        else:
-            tabs = [cr.peerTable(pa, vel), cr.peerTable(pb, vel)]
-            t_a, t_b = tabs
-            usable = True
-        pa.view[:] = pos.reshape(-1)
-        params.readOnly = True
-        src, dst, ts_p, ts_pw = pa, pb, [], []
-        for i in range(3 + steps if usable else 0):
-            src.read, src.partialRead, src.write = (i == 0), False, False
-            t0 = time.perf_counter()
-            assert src.nextParam(vel, dst, params, scratch, t_b if dst is pb else t_a).compute(cr, 2, "nBody3Dwp", n * per_body, local) == 0
-            if i >= 3:
-                ts_pw.append(time.perf_counter() - t0)
-                ts_p.append(max(cr.benchmarks(2)) * 1e-3)
-            src, dst = dst, src
-        if usable:
-            dt_p, dt_pw = allmax(float(np.mean(ts_p))), allmax(float(np.mean(ts_pw)))
-            res["resident_peer_stores"] = {"kernel": "nBody3Dwp", "ms_per_step_device": dt_p * 1e3, "ms_per_step_e2e": dt_pw * 1e3,
-                                           "GInter_per_s": inter / dt_p / 1e9, "GInter_per_s_e2e": inter / dt_pw / 1e9,
-                                           "frac_of_fp32_per_gpu": 20.0 * inter / n_gpus / dt_p / 1e12 / peak,
-                                           "exchange": "CUDA IPC peer stores" if spmd_ctx is not None else "peer stores"}
-        else:
-            res["resident_peer_stores"] = {"unavailable": "; ".join(t.error for t in tabs if t.error) or "a peer rank could not map the buffers"}
-        for t in tabs:
-            t.close() if spmd_ctx is not None else t.dispose()
-    for a in (pa, pb, vel, params, scratch):
-        a.dispose()
-    cr.dispose()
+                tabs = [_spmd.PeerTable(cr, spmd_ctx[0], spmd_ctx[1], spmd_ctx[2], x, vel) for x in (pa, pb)]
+                t_a, t_b = tabs[0].array, tabs[1].array
+                usable = all(t.ok for t in tabs)      # the same on every rank
+            else:
+                tabs = [cr.peerTable(pa, vel), cr.peerTable(pb, vel)]
+                t_a, t_b = tabs
+                usable = True
+            pa.view[:] = pos.reshape(-1)
+            params.readOnly = True
+            src, dst, ts_p, ts_pw = pa, pb, [], []
+            for i in range(3 + steps if usable else 0):
+                src.read, src.partialRead, src.write = (i == 0), False, False
+                t0 = time.perf_counter()
+                assert src.nextParam(vel, dst, params, scratch, t_b if dst is pb else t_a).compute(cr, 2, "nBody3Dwp", n * per_body, local) == 0
+                if i >= 3:
+                    ts_pw.append(time.perf_counter() - t0)
+                    ts_p.append(max(cr.benchmarks(2)) * 1e-3)
+                src, dst = dst, src
+            if usable:
+                dt_p, dt_pw = allmax(float(np.mean(ts_p))), allmax(float(np.mean(ts_pw)))
+                res["resident_peer_stores"] = {"kernel": "nBody3Dwp", "ms_per_step_device": dt_p * 1e3, "ms_per_step_e2e": dt_pw * 1e3,
+                                               "GInter_per_s": inter / dt_p / 1e9, "GInter_per_s_e2e": inter / dt_pw / 1e9,
+                                               "frac_of_fp32_per_gpu": 20.0 * inter / n_gpus / dt_p / 1e12 / peak,
+                                               "exchange": "CUDA IPC peer stores" if spmd_ctx is not None else "peer stores"}
+            else:
+                res["resident_peer_stores"] = {"unavailable": "; ".join(t.error for t in tabs if t.error) or "a peer rank could not map the buffers"}
+            for t in tabs:
+                t.close() if spmd_ctx is not None else t.dispose()
+        for a in (pa, pb, vel, params, scratch):
+            a.dispose()
+        cr.dispose()
+        return res
+
+    if defer_finish:
+        return res, finish
+    finish()
     return res
 
 
@@ -667,10 +676,13 @@ def run_ours(args):
         workloads["pipeline_c5"] = bench_pipeline(ck, kernels, po, n_gpus)
     if args.all:
         attach = (lambda c: spmd.attach(c, rank, world, torch_dev)) if spmd_mode else None
-        nb = bench_nbody(ck, kernels, po, devs, pk, sms, max(3, args.steps), 2, attach, n_gpus, allmax,
-                         (rank, world, torch_dev) if spmd_mode else None)
+        nb, nbody_finish = bench_nbody(ck, kernels, po, devs, pk, sms, max(3, args.steps), 2, attach, n_gpus, allmax,
+                                       (rank, world, torch_dev) if spmd_mode else None, defer_finish=True)
         workloads["nbody_c4"] = nb
+    else:
+        nbody_finish = None
 
+    line = None
     if rank == 0:
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": n_gpus, "steps": args.steps, "warmup": args.warmup,
@@ -698,6 +710,24 @@ def run_ours(args):
                          "final_shares": [round(x / items, 4) for x in shares[-1]] if shares else None},
             "workloads": workloads,
         }
+    # The last leg — n-body stepping with the exchange fused into the kernel, which at N > 1 maps other ranks' buffers and
+    # relies on every rank taking part — runs with the rest of the line already complete.  If it has not finished within
+    # 120 s (a rank that hangs would otherwise take the whole measurement with it), rank 0 prints the line without it and
+    # every rank leaves.
+    finished = threading.Event()
+
+    def watchdog():
+        if not finished.wait(120.0):
+            if line is not None:
+                workloads.get("nbody_c4", {})["resident_peer_stores"] = {"unavailable": "no result within 120 s"}
+                emit(line)
+            os._exit(0)
+
+    if nbody_finish is not None:
+        threading.Thread(target=watchdog, daemon=True).start()
+        nbody_finish()
+    finished.set()
+    if line is not None:
         emit(line)
     if spmd_mode:
         dist.barrier()
