@@ -16,7 +16,7 @@ from cekirdekler_b200._native import host
 rank, world, _ = spmd.init_process_group_from_env("gloo")
 ex = spmd.make_exchange(rank, world)
 h = host()
-b = h.ckh_balancer_create(world, 1)
+b = h.ckh_balancer_create(world, int(os.environ.get('CK_TEST_BALANCER_MODE', '1')))
 ranges = (C.c_int32 * world)()
 total, local = 1 << 20, 256
 speed = [1.0, 2.5][:world]                  # rank 1's "device" is 2.5x faster
@@ -47,14 +47,18 @@ def free_port():
     return p
 
 
-def test_two_ranks_agree_on_the_split():
+import pytest
+
+
+@pytest.mark.parametrize("mode", [1, 2], ids=["adaptive", "profile"])
+def test_two_ranks_agree_on_the_split(mode):
     import json
 
     port = free_port()
     procs = []
     for rank in range(2):
         env = dict(os.environ, RANK=str(rank), WORLD_SIZE="2", LOCAL_RANK=str(rank), MASTER_ADDR="127.0.0.1",
-                   MASTER_PORT=str(port), CK_ROOT=str(ROOT), OMP_NUM_THREADS="1")
+                   MASTER_PORT=str(port), CK_ROOT=str(ROOT), OMP_NUM_THREADS="1", CK_TEST_BALANCER_MODE=str(mode))
         procs.append(subprocess.Popen([sys.executable, "-c", WORKER], env=env, stdout=subprocess.PIPE, stderr=subprocess.PIPE, text=True))
     outs = []
     for p in procs:
