@@ -343,9 +343,10 @@ def bench_image_kernels(ck, kernels, po, dev, pk, sets=6, rounds=3):
         c.numberOfElementsPerWorkItem = 16
         S.append((a, b, c, h))
     calls = {"gaussianBlur": (lambda s: s[0].nextParam(s[1], dims), 1, n, 8.0 * n),
+             "gaussianBlur8": (lambda s: s[0].nextParam(s[1], dims), 4, n // 8, 8.0 * n),
              "sobel": (lambda s: s[1].nextParam(s[2], dims), 2, n, 8.0 * n),
              "histogram": (lambda s: s[2].nextParam(s[3]), 3, n // 16, 4.0 * n + 1024)}
-    names = {"gaussianBlur": "gaussianBlur", "sobel": "sobel", "histogram": "histogramZero histogram"}
+    names = {"gaussianBlur": "gaussianBlur", "gaussianBlur8": "gaussianBlur8", "sobel": "sobel", "histogram": "histogramZero histogram"}
     out = {}
     for k, (group, cid, rng_items, nbytes) in calls.items():
         ts = []

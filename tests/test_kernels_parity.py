@@ -423,3 +423,27 @@ def test_image_chain_bit_exact(gpus, W, H):
         assert sob.nextParam(hist).compute(cr, 3, "histogramZero histogram", n // 16, 256) == 0
     assert np.array_equal(hist.view, h_exp)
     assert int(hist.view.sum()) == n       # a checksum that holds at any size
+
+
+@pytest.mark.parametrize("W,H", [(256, 128), (3840, 2160), (24, 7)])
+def test_gaussian_blur8_is_bit_identical_to_the_one_pixel_kernel(gpus, W, H):
+    """gaussianBlur8: eight adjacent pixels per work-item with 16-byte loads; same operations per pixel, so the same bits
+    as gaussianBlur and the oracle — split over every device (8 floats of `out` per work-item), including a frame so
+    narrow that most work-items take the clamped edge path."""
+    n = W * H
+    img = po.uniform(0xBEEF, n, 0, 1)
+    exp = np.zeros(n, np.float32)
+    po.blur5x5(img, exp, np.array([W, H], np.int32))
+    devs = all_gpus() if (n // 8) % (64 * gpus) == 0 else gpu0()
+    cr = ck.ClNumberCruncher(devs, kernels.source("image"))
+    assert cr.errorCode() == 0, cr.errorMessage()
+    src, out, dims = ck.ClFloatArray(n), ck.ClFloatArray(n), ck.ClIntArray(2)
+    src.view[:] = img
+    dims.view[:] = [W, H]
+    dims.readOnly = True
+    src.readOnly = True
+    out.writeOnly = True
+    out.numberOfElementsPerWorkItem = 8
+    local = 64 if (n // 8) % 64 == 0 else (n // 8)
+    assert src.nextParam(out, dims).compute(cr, 1, "gaussianBlur8", n // 8, local) == 0
+    assert np.array_equal(out.view, exp)
