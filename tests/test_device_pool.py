@@ -101,15 +101,21 @@ def test_broadcast_then_device_resident_use(gpus):
     pool.dispose()
 
 
-def test_device_select_and_serial_mode_keep_a_run_on_one_device(gpus):
-    """A SELECT_BEGIN..SELECT_END (or SERIAL_MODE) run works on device-resident data, which only holds together if all of
-    its tasks land on the same device, in order."""
-    pool = ClDevicePool(ClDevicePoolType.DEVICE_COMPUTE_AT_WILL, SRC, True, 3)
+@pytest.mark.parametrize("fine", [False, True], ids=["blocking", "fineGrained"])
+def test_device_select_and_serial_mode_keep_a_run_on_one_device(gpus, fine):
+    """A run of tasks works on device-resident data (upload in the first task, download in the last), which only holds
+    together if all of its tasks land on the same device, in order.  SERIAL_MODE promises both in every pool.
+    DEVICE_SELECT promises the device only: a fine-grained pool spreads the tasks of such a run over its queues, as the
+    reference does (ClPipeline.cs:4946-4950 switches the round-robin off for serial mode alone), so ordered
+    DEVICE_SELECT runs are checked in the blocking pool, where the single consumer of the device keeps them in order."""
+    pool = ClDevicePool(ClDevicePoolType.DEVICE_COMPUTE_AT_WILL, SRC, fine, 3)
     pool.addDevice(devices())
     tp = ClTaskPool()
     results = []
-    for run, (begin, end) in enumerate([(ClTaskType.TASK_MESSAGE_DEVICE_SELECT_BEGIN, ClTaskType.TASK_MESSAGE_DEVICE_SELECT_END),
-                                        (ClTaskType.TASK_MESSAGE_SERIAL_MODE_BEGIN, ClTaskType.TASK_MESSAGE_SERIAL_MODE_END)] * 3):
+    kinds = [(ClTaskType.TASK_MESSAGE_SERIAL_MODE_BEGIN, ClTaskType.TASK_MESSAGE_SERIAL_MODE_END)]
+    if not fine:
+        kinds.append((ClTaskType.TASK_MESSAGE_DEVICE_SELECT_BEGIN, ClTaskType.TASK_MESSAGE_DEVICE_SELECT_END))
+    for run, (begin, end) in enumerate(kinds * 3):
         a = ck.ClArray(N, np.int32)
         a.view[:] = run
         for s in range(4):
