@@ -141,3 +141,10 @@ def test_cruncher_without_kernels_or_devices_is_inert():
     a = ck.ClArray(1024, np.float32)
     assert a.compute(cr, 1, "f", 1024, 256) != 0   # refused, not raised
     assert cr.numberOfErrorsHappened >= 1
+
+
+def test_numa_preference_helper_never_raises():
+    from cekirdekler_b200 import spmd
+
+    info = spmd.prefer_host_memory_near_gpu(0)       # no NVML / single node here: reports and leaves the policy alone
+    assert set(info) >= {"numa_node", "applied"} and info["applied"] in (True, False)
