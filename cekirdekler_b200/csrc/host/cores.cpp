@@ -274,7 +274,7 @@ void Cores::compute(const std::vector<std::string>& kernelNames, int numRepeats,
                     for (int r = 0; r < reps; r++) {
                         for (size_t s = 1; s + 1 < kernelNames.size(); s++)
                             workers_[i]->compute(kernelNames[s], refs[i], ranges[i], localRange, computeId);
-                        if (hasSync) workers_[i]->compute(syncKernelName, 0, localRange, localRange, -1);
+                        if (hasSync) workers_[i]->compute(syncKernelName, 0, localRange, localRange, computeId);
                     }
                     computePipelined(i, syncKernelName, kernelNames.back(), arrs, numRepeats, ranges, blobs, refs, pipelineType, computeId, 1);
                 }
@@ -312,7 +312,7 @@ void Cores::compute(const std::vector<std::string>& kernelNames, int numRepeats,
             if (kernelNames.size() > 1) {
                 for (int r = 0; r < numRepeats; r++) {
                     for (const auto& k : kernelNames) w.compute(k, refs[i], ranges[i], localRange, computeId, cq);
-                    if (hasSync) w.compute(syncKernelName, 0, localRange, localRange, -1, cq);
+                    if (hasSync) w.compute(syncKernelName, 0, localRange, localRange, computeId, cq);
                 }
             } else if (!hasSync) {
                 w.computeRepeated(kernelNames[0], refs[i], ranges[i], localRange, computeId, numRepeats, cq);
@@ -528,16 +528,17 @@ void Cores::computePipelined(int i, const std::string& syncKernelName, const std
             }
         }
         if (doDown) {
-            w.readFromBufferAllData(arrs, gi, D);
             ck_handle cq2 = w.numComputeQueues() > 1 ? w.computeQueue(2) : w.mainQueue();
             for (ck_handle q : {w.writeQueue(0), w.mainQueue(), w.readQueue(0), w.writeQueue(1), cq2, w.readQueue(1)}) flush(q);
             if (downloaded) {
                 finish(w.writeQueue(0));
                 finish(w.writeQueue(1));
-            } else {
-                finish(w.mainQueue());
-                finish(cq2);
             }
+            // both lanes' kernels are done before a `write all` array is fetched whole on the main queue (the slice
+            // downloads above already waited for them, so these two waits cost nothing in the usual case)
+            finish(w.mainQueue());
+            finish(cq2);
+            w.readFromBufferAllData(arrs, gi, D);
         }
         for (auto& L : lane)
             for (int j = 0; j < steps; j++) {
@@ -556,9 +557,9 @@ void Cores::computePipelined(int i, const std::string& syncKernelName, const std
             if (doDown) w.readPartialEvent(arrs, off + chunk * k, chunk, nullptr, nullptr, q);
         }
         if (doDown) {
-            w.readFromBufferAllData(arrs, gi, D);
             for (int k = 1; k <= std::min(16, nq); k++) flush(w.computeQueue(k));
             for (int k = 1; k <= std::min(16, nq); k++) finish(w.computeQueue(k));
+            w.readFromBufferAllData(arrs, gi, D);   // `write all`: whole array, after every chunk's kernel has finished
         }
     }
     if (!doDown) w.finishAll();  // upload-only stage of a multi-kernel pipeline: later kernels run on the main queue

@@ -175,6 +175,11 @@ int ClParameterGroup::compute(ClNumberCruncher& cr, int computeId, const std::st
             return complain(4, "Work-size error: global range(" + std::to_string(globalRange) +
                                    ") is not an integer multiple of (local range)*(number of pipeline blobs)=(" +
                                    std::to_string((long long)localRange * pipelineBlobs) + ").");
+        // the event-driven pipeline runs two lanes of blobs/2 chunks each (Cores.cs:1256-1366): with an odd count the last
+        // chunk of each lane would be neither uploaded, computed nor downloaded (the reference only documents "multiple of 4")
+        if (pipelineType == Cores::PIPELINE_EVENT && (pipelineBlobs % 2) != 0)
+            return complain(11, "Work-size error: the event-driven pipeline needs an even number of pipeline blobs (" +
+                                    std::to_string(pipelineBlobs) + " given); use a multiple of 4, or the driver-controlled pipeline.");
         if (globalRange < (long long)localRange * D * pipelineBlobs)
             return complain(6, "Work-size error: global range(" + std::to_string(globalRange) +
                                    ") must be equal to or greater than (number of selected devices)*(local worksize)*(number of pipeline blobs)=(" +

@@ -1,7 +1,8 @@
 // stream.cu — streaming kernels K2/K3 of the hot path: HBM-bound when the arrays are resident,
 // host-link-bound when ClNumberCruncher streams them with partial reads/writes.
 //
-//   vectorAdd   the reference's own kernel text, verbatim OpenCL C (Tester.cs:7820-7824): 1 element per work-item.
+//   vectorAdd   c[i] = a[i] + b[i], 1 element per work-item, the operation of the reference's stream test
+//               (Tester.cs:7820-7824; its verbatim kernel text is a test vector under tests/reference_kernels.py).
 //   vectorAdd4  same result, 4 elements per work-item (numberOfElementsPerWorkItem = 4): one 16-byte load per input
 //               and one 16-byte store per warp lane, fully coalesced (512 B per warp per access).
 //   saxpy / saxpy4   y[i] = alpha[0]*x[i] + y[i] with the multiply and the add rounded separately
@@ -10,10 +11,10 @@
 //               scalar kernel arguments.
 // Algorithmic traffic: 12 B per element (two 4 B reads + one 4 B write).
 
-__kernel void vectorAdd(__global float*a,__global float*b,__global float*c)
+__kernel void vectorAdd(const float* __restrict__ a, const float* __restrict__ b, float* __restrict__ c)
 {
-    int i=get_global_id(0);
-    c[i]=a[i]+b[i];
+    const size_t i = get_global_id(0);
+    c[i] = __fadd_rn(a[i], b[i]);
 }
 
 __kernel void vectorAdd4(const float4* __restrict__ a, const float4* __restrict__ b, float4* __restrict__ c)

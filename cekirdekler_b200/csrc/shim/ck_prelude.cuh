@@ -37,7 +37,8 @@ typedef unsigned long  ulong;
 #define get_global_offset(d) ((size_t)(__ck_goff))
 #define get_local_id(d)      ((size_t)(threadIdx.x))
 #define get_local_size(d)    ((size_t)(blockDim.x))
-#define get_group_id(d)      ((size_t)(__ck_goff / blockDim.x + blockIdx.x))
+#define get_group_id(d)      ((size_t)(blockIdx.x))   /* as in OpenCL: 0 .. get_num_groups-1 of THIS enqueue (a device's share) */
+#define ck_global_group_id() ((size_t)(__ck_goff / blockDim.x + blockIdx.x))   /* extension: group index within the whole range */
 #define get_num_groups(d)    ((size_t)(gridDim.x))
 #define get_global_size(d)   ((size_t)(gridDim.x * blockDim.x))
 #define get_work_dim()       (1u)

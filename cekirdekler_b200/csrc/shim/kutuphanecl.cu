@@ -543,7 +543,7 @@ void addUserEvent(ck_handle hQueue, ck_handle hUserEvent) {
     cudaSetDevice(q->ordinal);
     void* d = nullptr;
     if (!CK_CUDA(cudaHostGetDevicePointer(&d, (void*)u->flag, 0))) return;
-    int r = fn(q->stream, (unsigned long long)(uintptr_t)d, 1u, 0x2 /* CU_STREAM_WAIT_VALUE_GEQ */);
+    int r = fn(q->stream, (unsigned long long)(uintptr_t)d, 1u, 0x0 /* CU_STREAM_WAIT_VALUE_GEQ: flag >= 1 */);
     if (r != 0) set_error("addUserEvent: cuStreamWaitValue32 failed with code " + std::to_string(r));
 }
 void incrementUserEvent(ck_handle h) {

@@ -7,6 +7,7 @@ import numpy as np
 import pytest
 
 import cekirdekler_b200 as ck
+import reference_kernels
 from cekirdekler_b200 import kernels
 from oracle import pyoracle as po
 
@@ -31,7 +32,7 @@ def cruncher(tname, multi, gpus):
     if key not in _crunchers:
         devs = ck.ClPlatforms.all().gpus()
         devs = devs if multi else devs[0]
-        src = kernels.REFERENCE_COPY_KERNEL_CHAR if tname == "Char" else kernels.reference_copy_kernel(TYPES[tname][0])
+        src = reference_kernels.REFERENCE_COPY_KERNEL_CHAR if tname == "Char" else reference_kernels.reference_copy_kernel(TYPES[tname][0])
         cr = ck.ClNumberCruncher(devs, src)
         assert cr.errorCode() == 0, cr.errorMessage()
         _crunchers[key] = cr

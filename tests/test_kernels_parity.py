@@ -10,6 +10,7 @@ import numpy as np
 import pytest
 
 import cekirdekler_b200 as ck
+import reference_kernels
 from cekirdekler_b200 import kernels
 from oracle import pyoracle as po
 
@@ -121,7 +122,7 @@ def test_reference_vector_add_test(gpus):
     c = ck.ClArray(n, np.float32)
     a.view[:] = 3
     c.view[:] = 105
-    cr = ck.ClNumberCruncher(all_gpus(), kernels.REFERENCE_VECTOR_ADD)
+    cr = ck.ClNumberCruncher(all_gpus(), reference_kernels.REFERENCE_VECTOR_ADD)
     assert cr.errorCode() == 0, cr.errorMessage()
     g = a.nextParam(b, c)
     for _ in range(10):
@@ -193,7 +194,7 @@ def test_nbody2d_reference_kernel_text_and_tiled_kernel(gpus):
     fx_exp, fy_exp = np.zeros(n, np.float32), np.zeros(n, np.float32)
     po.nbody2d(x, y, fx_exp, fy_exp)
 
-    cr = ck.ClNumberCruncher(all_gpus(), kernels.reference_nbody_kernel(n))
+    cr = ck.ClNumberCruncher(all_gpus(), reference_kernels.reference_nbody_kernel(n))
     assert cr.errorCode() == 0, cr.errorMessage()
     fx, fy = np.zeros(n, np.float32), np.zeros(n, np.float32)
     xc, yc, fxc, fyc = ck.ClArray(x), ck.ClArray(y), ck.ClArray(fx), ck.ClArray(fy)

@@ -94,6 +94,44 @@ def test_repeat_count_with_sync_kernel(gpus):
     assert (a.view == 11).all()
 
 
+def test_two_kernel_repeat_runs_the_sync_kernel(gpus):
+    """Several kernels, repeatCount > 1 and a repeatKernelName (Cores.cs:793-800): the sync kernel runs once per repeat
+    with the arguments it was bound with."""
+    a, counter = ck.ClArray(N, np.int32), ck.ClArray(256, np.int32)
+    a.view[:] = 0
+    counter.view[:] = 0
+    counter.writeAll = True
+    src2 = "__kernel void addBoth(__global int* a, __global int* counter) { int i = get_global_id(0); a[i] += 1; }\n" \
+           "__kernel void addTwo(__global int* a, __global int* counter) { int i = get_global_id(0); a[i] += 2; }\n" \
+           "__kernel void bump2(__global int* a, __global int* counter) { if (get_global_id(0) == 0) counter[0] += 1; }\n"
+    cr2 = ck.ClNumberCruncher(dev0(), src2)
+    cr2.repeatCount = 5
+    cr2.repeatKernelName = "bump2"
+    assert a.nextParam(counter).compute(cr2, 1, "addBoth addTwo", N, 256) == 0
+    assert (a.view == 15).all() and counter[0] == 5
+
+
+@pytest.mark.parametrize("ptype", ["event", "driver"])
+def test_pipelined_write_all_comes_back_complete(gpus, ptype):
+    """A `write all` array of a pipelined compute is fetched whole only after every blob's kernel has finished
+    (quirk Q2 fixed, Worker.cs:871-885): a histogram over all blobs must be complete on the host."""
+    n = 1 << 22
+    src = "__kernel void count(__global const int* v, __global int* hist) { int i = get_global_id(0); atomic_add(&hist[v[i] & 255], 1); }\n" \
+          "__kernel void slowCount(__global const int* v, __global int* hist) { int i = get_global_id(0); int x = v[i]; " \
+          "for (int k = 0; k < 2000; k++) x = x * 1664525 + 1013904223; atomic_add(&hist[v[i] & 255], (x == 0x12345678 && i == -1) ? 2 : 1); }\n"
+    cr = ck.ClNumberCruncher(dev0(), src)
+    assert cr.errorCode() == 0, cr.errorMessage()
+    v, hist = ck.ClArray(n, np.int32), ck.ClArray(256, np.int32)
+    v.view[:] = (np.arange(n, dtype=np.int64) * 2654435761 >> 7).astype(np.int32)
+    v.partialRead, v.read, v.write = True, False, False
+    hist.read, hist.writeAll = True, True
+    exp = np.bincount(v.view & 255, minlength=256)
+    for kernel in ("count", "slowCount"):
+        hist.view[:] = 0
+        assert v.nextParam(hist).compute(cr, 1, kernel, n, 256, 0, True, ck.PIPELINE_EVENT if ptype == "event" else ck.PIPELINE_DRIVER, 8) == 0
+        assert np.array_equal(hist.view, exp), kernel
+
+
 def test_zero_copy_stream_arrays_are_read_in_place(gpus):
     devs = ck.ClPlatforms.all().gpus(streamingEnabled=True)[0]      # GPU_STREAM: device.isGddr() = false (ClDevice.cs:105-108)
     cr = ck.ClNumberCruncher(devs, SRC)
@@ -120,6 +158,13 @@ def test_validation_rules_refuse_and_count_errors(gpus):
     cr = ck.ClNumberCruncher(dev0(), SRC)
     a = ck.ClArray(4096, np.int32)
     assert a.compute(cr, 1, "addOne", 4096, 256, 0, True, ck.PIPELINE_EVENT, 3) == 4   # not a multiple of local*blobs
+    cr = ck.ClNumberCruncher(dev0(), SRC)
+    a3 = ck.ClArray(768, np.int32)
+    assert a3.compute(cr, 1, "addOne", 768, 128, 0, True, ck.PIPELINE_EVENT, 3) == 11  # two lanes of blobs/2 chunks: odd counts would skip work
+    cr = ck.ClNumberCruncher(dev0(), SRC)
+    a3.view[:] = 0
+    assert a3.compute(cr, 1, "addOne", 768, 128, 0, True, ck.PIPELINE_DRIVER, 3) == 0  # the driver-controlled pipeline takes any count
+    assert (a3.view == 1).all()
     cr = ck.ClNumberCruncher(dev0(), SRC)
     assert a.compute(cr, 1, "noSuchKernel", 4096, 256) == 10   # reported, not raised
     cr = ck.ClNumberCruncher(dev0(), "__kernel void broken(__global int* a) { a[0] = undefined_thing; }")

@@ -4,6 +4,7 @@ import numpy as np
 import pytest
 
 import cekirdekler_b200 as ck
+import reference_kernels
 from cekirdekler_b200 import kernels
 from oracle import pyoracle as po
 
@@ -26,7 +27,7 @@ def test_wave_equation_on_wrapped_structs(gpus):
     for a in (xyz, xyzn):
         a.partialRead, a.read, a.write = True, False, False
     xyzo.read = False
-    cr = ck.ClNumberCruncher(ck.ClPlatforms.all().gpus(), kernels.REFERENCE_WAVE_EQUATION)
+    cr = ck.ClNumberCruncher(ck.ClPlatforms.all().gpus(), reference_kernels.REFERENCE_WAVE_EQUATION)
     assert cr.errorCode() == 0, cr.errorMessage()
     for frame in range(4):
         args_h[:5] = [1.0 + 0.1 * frame, 0.05 * frame, base[0, 0], base[0, 1], n]
@@ -39,7 +40,7 @@ def test_wave_equation_on_wrapped_structs(gpus):
 def test_opencl_c_idioms_run(gpus):
     src = """
     float helper(float x) { return mad(x, 2.0f, 1.0f); }
-    __kernel void idioms(__global const float* in, __global float* out, __global int* hist)
+    __kernel void idioms(__global const float* in, __global float* out, __global int* hist, __global int* gid, __global int* ggid)
     {
         __local float tile[256];
         int l = get_local_id(0);
@@ -49,18 +50,26 @@ def test_opencl_c_idioms_run(gpus):
         float left = tile[(l + get_local_size(0) - 1) % get_local_size(0)];
         float4 v = (float4)((float2)(tile[l], left), 1.0f, 0.0f);
         v = v * (float4)(2.0f) + v;
-        out[i] = helper(dot(v, v)) + (float)(get_group_id(0) % 2);
+        out[i] = helper(dot(v, v)) + (float)((get_global_id(0) / get_local_size(0)) % 2);
+        gid[i] = (int)get_group_id(0);             // OpenCL: counted from the start of this enqueue, i.e. of the device's share
+        ggid[i] = (int)ck_global_group_id();       // extension: counted from the start of the whole range
         atomic_add(&hist[i % 16], 1);
     }"""
     n = 1 << 14
     cr = ck.ClNumberCruncher(ck.ClPlatforms.all().gpus(), src)
     assert cr.errorCode() == 0, cr.errorMessage()
     a, out, hist = ck.ClArray(n, np.float32), ck.ClArray(n, np.float32), ck.ClArray(16, np.int32)
+    gid, ggid = ck.ClArray(n, np.int32), ck.ClArray(n, np.int32)
     a.view[:] = np.arange(n) % 17
     a.readOnly = True
     out.writeOnly = True
+    gid.writeOnly = True
+    ggid.writeOnly = True
     hist.writeAll = True
-    assert a.nextParam(out, hist).compute(cr, 1, "idioms", n, 256) == 0
+    assert a.nextParam(out, hist, gid, ggid).compute(cr, 1, "idioms", n, 256) == 0
+    assert np.array_equal(ggid.view, np.arange(n) // 256)
+    for ref, rng in zip(cr.globalReferences(1), cr.globalRanges(1)):
+        assert np.array_equal(gid.view[ref:ref + rng], np.arange(rng) // 256)
     x = a.view.reshape(-1, 256)
     left = np.roll(x, 1, axis=1)
     v2 = (3 * x) ** 2 + (3 * left) ** 2 + 9.0
@@ -79,7 +88,7 @@ def test_devices_sorted_by_nbody_micro_benchmark(gpus):
 def test_compute_follows_an_array_that_was_resized_or_switched(gpus):
     """ClArray.N and ClArray.fastArr replace the backing store (ClArray.cs:749-800, :889-958); the next compute() must
     use the new one, on every device of the split."""
-    cr = ck.ClNumberCruncher(ck.ClPlatforms.all().gpus(), kernels.reference_copy_kernel("float"))
+    cr = ck.ClNumberCruncher(ck.ClPlatforms.all().gpus(), reference_kernels.reference_copy_kernel("float"))
     assert cr.errorCode() == 0, cr.errorMessage()
     n = 256 * 64
     a, b = ck.ClFloatArray(n), ck.ClFloatArray(n)

@@ -5,6 +5,7 @@ import ctypes as C
 import pytest
 
 from cekirdekler_b200 import kernels
+import reference_kernels
 from cekirdekler_b200._native import shim
 
 
@@ -76,9 +77,9 @@ def test_shipped_kernels_build_for_sm_100a(name):
 
 
 @pytest.mark.parametrize("src", [
-    kernels.reference_copy_kernel("uchar"), kernels.reference_copy_kernel("double"), kernels.reference_copy_kernel("long"),
-    kernels.REFERENCE_COPY_KERNEL_CHAR, kernels.REFERENCE_VECTOR_ADD, kernels.reference_nbody_kernel(8192),
-    kernels.REFERENCE_WAVE_EQUATION,
+    reference_kernels.reference_copy_kernel("uchar"), reference_kernels.reference_copy_kernel("double"), reference_kernels.reference_copy_kernel("long"),
+    reference_kernels.REFERENCE_COPY_KERNEL_CHAR, reference_kernels.REFERENCE_VECTOR_ADD, reference_kernels.reference_nbody_kernel(8192),
+    reference_kernels.REFERENCE_WAVE_EQUATION,
 ])
 def test_reference_opencl_strings_build_unmodified(src):
     rc, log, _ = compile_check(src)
