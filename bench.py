@@ -116,9 +116,9 @@ class ClockSampler:
         return {"sm_mhz": float(np.median(self.samples)), "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons)}
 
 
-def ncu_traffic(kernel):
-    """DRAM bytes per launch of `kernel` from the committed `ncu --set full` capture (profiles/r1_ncu_summary.json), or None."""
-    f = ROOT / "profiles" / "r1_ncu_summary.json"
+def ncu_traffic(kernel, summary="r1_ncu_summary.json"):
+    """DRAM bytes per launch of `kernel` from the committed `ncu --set full` capture (profiles/<summary>), or None."""
+    f = ROOT / "profiles" / summary
     try:
         return float(json.loads(f.read_text())[kernel]["traffic_B"])
     except Exception:
@@ -189,39 +189,61 @@ def first_stable(imb, tol=1.05, hold=3):
     return None
 
 
-def bench_hostlink(L, ordinal=0, mib=512, reps=4):
-    """Host-link roofline for the streamed workloads: pinned H2D, D2H and both at once, through the C ABI's own transfers."""
-    import ctypes as C
-
+def bench_hostlink(L, ordinals=(0,), mib=512, reps=4, barrier=None):
+    """Host-link roofline for the streamed workloads: pinned H2D, D2H and both at once, through the C ABI's own transfers, on
+    every device of `ordinals` AT THE SAME TIME (one pinned array pair, one queue pair per device).  With one process per
+    GPU every rank calls this with its own device and `barrier`, so that all ranks copy together; the caller sums the ranks.
+    Returns this process's aggregate GB/s and the per-device figures."""
     n = mib * (1 << 20) // 4
     lst = L.platformList()
     plat = L.createPlatform(lst, 0)
     L.deletePlatformList(lst)
-    dev = L.createDevice(plat, L.CODE_GPU(), ordinal)
-    ctx = L.createContext(plat, dev)
-    q1, q2 = L.createCommandQueue(ctx, dev, 0), L.createCommandQueue(ctx, dev, 0)
-    a1, a2 = L.createArray(n, 4096, 0), L.createArray(n, 4096, 0)
-    h1, h2 = L.alignedArrHead(a1), L.alignedArrHead(a2)
-    b1, b2 = L.createBuffer(ctx, n, 0, 0, h1, 1, 0, 0), L.createBuffer(ctx, n, 0, 0, h2, 1, 0, 0)
-    out = {}
+    devs = []
+    for o in ordinals:
+        dev = L.createDevice(plat, L.CODE_GPU(), o)
+        ctx = L.createContext(plat, dev)
+        q1, q2 = L.createCommandQueue(ctx, dev, 0), L.createCommandQueue(ctx, dev, 0)
+        a1, a2 = L.createArray(n, 4096, 0), L.createArray(n, 4096, 0)
+        h1, h2 = L.alignedArrHead(a1), L.alignedArrHead(a2)
+        b1, b2 = L.createBuffer(ctx, n, 0, 0, h1, 1, 0, 0), L.createBuffer(ctx, n, 0, 0, h2, 1, 0, 0)
+        devs.append(dict(dev=dev, ctx=ctx, q1=q1, q2=q2, a1=a1, a2=a2, h1=h1, h2=h2, b1=b1, b2=b2))
+    sync = barrier or (lambda: None)
+
+    def drain():
+        for d in devs:
+            L.finish(d["q1"]), L.finish(d["q2"])
 
     def timed(fn):
-        fn()
-        L.finish(q1), L.finish(q2)
+        """Seconds per repetition for the whole set, and per device (each device's own queues drained in turn)."""
+        for d in devs:
+            fn(d)
+        drain()
+        sync()
         t0 = time.perf_counter()
         for _ in range(reps):
-            fn()
-        L.finish(q1), L.finish(q2)
-        return (time.perf_counter() - t0) / reps
+            for d in devs:
+                fn(d)
+        per = []
+        for d in devs:
+            L.finish(d["q1"]), L.finish(d["q2"])
+            per.append((time.perf_counter() - t0) / reps)
+        sync()
+        return (time.perf_counter() - t0) / reps, per
 
     byts = n * 4
-    out["h2d_GBps"] = byts / timed(lambda: L.writeToBuffer(q1, b1, h1)) / 1e9
-    out["d2h_GBps"] = byts / timed(lambda: L.readFromBuffer(q2, b2, h2)) / 1e9
-    t = timed(lambda: (L.writeToBuffer(q1, b1, h1), L.readFromBuffer(q2, b2, h2)))
-    out["bidirectional_each_GBps"] = byts / t / 1e9
-    for h, f in ((b1, L.deleteBuffer), (b2, L.deleteBuffer), (a1, L.deleteArray), (a2, L.deleteArray), (q1, L.deleteCommandQueue),
-                 (q2, L.deleteCommandQueue), (ctx, L.deleteContext), (dev, L.deleteDevice), (plat, L.deletePlatform)):
-        f(h)
+    out = {"devices": list(ordinals), "MiB_per_copy": mib}
+    for key, fn in (("h2d", lambda d: L.writeToBuffer(d["q1"], d["b1"], d["h1"])),
+                    ("d2h", lambda d: L.readFromBuffer(d["q2"], d["b2"], d["h2"])),
+                    ("bidirectional_each", lambda d: (L.writeToBuffer(d["q1"], d["b1"], d["h1"]), L.readFromBuffer(d["q2"], d["b2"], d["h2"])))):
+        t, per = timed(fn)
+        out[key + "_GBps"] = byts * len(devs) / t / 1e9          # aggregate over this process's devices
+        if len(devs) > 1:
+            out[key + "_GBps_per_device"] = [round(byts / p / 1e9, 2) for p in per]
+    for d in devs:
+        for h, f in ((d["b1"], L.deleteBuffer), (d["b2"], L.deleteBuffer), (d["a1"], L.deleteArray), (d["a2"], L.deleteArray),
+                     (d["q1"], L.deleteCommandQueue), (d["q2"], L.deleteCommandQueue), (d["ctx"], L.deleteContext), (d["dev"], L.deleteDevice)):
+            f(h)
+    L.deletePlatform(plat)
     return out
 
 
@@ -235,49 +257,27 @@ def bench_pipeline(ck, kernels, po, n_gpus, frames=24):
     n = Wf * Hf
     devs = ck.ClPlatforms.all().gpus()
     d = lambda i: devs[i % max(1, n_gpus)]
-    src = kernels.source("image") + """
-    __kernel void blurStage(const float* in, const int* dims, float* out, int* dimsOut) {
-        const size_t p = get_global_id(0);
-        if (p < 2) dimsOut[p] = dims[p];
-        const int W = dims[0], H = dims[1];
-        if (W <= 0 || H <= 0) return;
-        const int y = (int)(p / (unsigned)W), x = (int)(p - (size_t)y * W);
-        const float c = ck_blur_h(in, W, x, y);
-        const float s1 = __fadd_rn(ck_blur_h(in, W, x, ck_clampi(y - 1, 0, H - 1)), ck_blur_h(in, W, x, ck_clampi(y + 1, 0, H - 1)));
-        const float s2 = __fadd_rn(ck_blur_h(in, W, x, ck_clampi(y - 2, 0, H - 1)), ck_blur_h(in, W, x, ck_clampi(y + 2, 0, H - 1)));
-        out[p] = __fmul_rn(0.00390625f, __fmaf_rn(6.0f, c, __fmaf_rn(4.0f, s1, s2)));
-    }
-    __kernel void sobelStage(const float* in, const int* dims, float* out) {
-        const int W = dims[0], H = dims[1];
-        if (W <= 0 || H <= 0) return;
-        const size_t p = get_global_id(0);
-        const int y = (int)(p / (unsigned)W), x = (int)(p - (size_t)y * W);
-        const int xm = ck_clampi(x - 1, 0, W - 1), xp = ck_clampi(x + 1, 0, W - 1);
-        const int ym = ck_clampi(y - 1, 0, H - 1), yp = ck_clampi(y + 1, 0, H - 1);
-        const float* rm = in + (size_t)ym * W; const float* r0 = in + (size_t)y * W; const float* rp = in + (size_t)yp * W;
-        const float right = __fmaf_rn(2.0f, r0[xp], __fadd_rn(rm[xp], rp[xp]));
-        const float left = __fmaf_rn(2.0f, r0[xm], __fadd_rn(rm[xm], rp[xm]));
-        const float bottom = __fmaf_rn(2.0f, rp[x], __fadd_rn(rp[xm], rp[xp]));
-        const float top = __fmaf_rn(2.0f, rm[x], __fadd_rn(rm[xm], rm[xp]));
-        const float gx = __fsub_rn(right, left), gy = __fsub_rn(bottom, top);
-        out[p] = __fsqrt_rn(__fmaf_rn(gx, gx, __fmul_rn(gy, gy)));
-    }"""
+    RB = 30
+    src = kernels.image_pipeline_source()
+    gs, ls = kernels.strip_launch(Wf, Hf, RB)
     frame = ck.ClFloatArray(n)
     frame.view[:] = po.uniform(0xF00D, n, 0, 1)
-    dims = np.array([Wf, Hf], np.int32)
+    dims = np.array([Wf, Hf, RB], np.int32)
+    dims2 = np.array([Wf, Hf], np.int32)
     b, s, hexp = np.zeros(n, np.float32), np.zeros(n, np.float32), np.zeros(256, np.uint32)
-    po.blur5x5(frame.view, b, dims)
-    po.sobel(b, s, dims)
+    po.blur5x5(frame.view, b, dims2)
+    po.sobel(b, s, dims2)
     po.histogram(s, hexp)
     out = {"frame": f"{Wf}x{Hf} float", "stages_on": [d(i).ordinals[0] for i in range(3)]}
     for host_fwd in (False, True):
         blur, sob, hist = ClPipelineStage(), ClPipelineStage(), ClPipelineStage()
-        blur.addDevices(d(0)); blur.addKernels(src, "blurStage", [n], [256])
-        blur.addInputBuffers((np.float32, n), (np.int32, 2)); blur.addOutputBuffers((np.float32, n), (np.int32, 2))
-        sob.addDevices(d(1)); sob.addKernels(src, "sobelStage", [n], [256])
-        sob.addInputBuffers((np.float32, n), (np.int32, 2)); sob.addOutputBuffers((np.float32, n)); sob.appendToStage(blur)
-        hist.addDevices(d(2)); hist.addKernels(src, "histogramZero histogram", [n // 16, n // 16], [256, 256])
-        hist.addInputBuffers((np.float32, n, 16)); hist.addOutputBuffers((np.uint32, 256)); hist.appendToStage(sob)
+        blur.addDevices(d(0)); blur.addKernels(src, "blurStage", [gs], [ls])
+        blur.addInputBuffers((np.float32, n), (np.int32, 3)); blur.addOutputBuffers((np.float32, n), (np.int32, 3))
+        sob.addDevices(d(1)); sob.addKernels(src, "sobelStage", [gs], [ls])
+        sob.addInputBuffers((np.float32, n), (np.int32, 3)); sob.addOutputBuffers((np.float32, n), (np.int32, 3)); sob.appendToStage(blur)
+        hist.addDevices(d(2)); hist.addKernels(src, "histStage", [592 * 256], [256])
+        hist.addInputBuffers((np.float32, n), (np.int32, 3)); hist.addHiddenBuffers((np.uint32, 2049))
+        hist.addOutputBuffers((np.uint32, 256)); hist.appendToStage(sob)
         pipe = hist.makePipeline(hostForwarding=host_fwd)
         assert pipe.errorCode() == 0, pipe.errorMessage()
         res = np.zeros(256, np.uint32)
@@ -288,91 +288,191 @@ def bench_pipeline(ck, kernels, po, n_gpus, frames=24):
         for _ in range(frames):
             pipe.pushData([frame.view, dims], [res])         # mode B: every frame comes from (pinned) host memory
         dt = (time.perf_counter() - t0) / frames
-        key = "host_bounce" if host_fwd else "nvlink_p2p"
+        one_device = len(set(out["stages_on"])) == 1       # then the "hand-off" is a copy inside one GPU's HBM, not NVLink
+        key = "host_bounce" if host_fwd else ("device_copy_same_gpu" if one_device else "nvlink_p2p")
         out[key] = {"frames_per_s": 1.0 / dt, "ms_per_frame": dt * 1e3, "histogram_exact": ok and bool(np.array_equal(res, hexp))}
         if not host_fwd:
             t0 = time.perf_counter()
             for _ in range(frames):
                 pipe.pushData()                              # mode A: frames already resident on the first device
             dt = (time.perf_counter() - t0) / frames
-            out["nvlink_p2p_resident"] = {"frames_per_s": 1.0 / dt, "ms_per_frame": dt * 1e3,
+            out[key + "_resident"] = {"frames_per_s": 1.0 / dt, "ms_per_frame": dt * 1e3,
                                           "GBps_algorithmic_hbm": 165.9e6 / dt / 1e9}
         pipe.dispose()
     # task pool: independent frames (blur only), greedy over the devices
+    from cekirdekler_b200.pool import ClTaskType
+
     pool = ClDevicePool(ClDevicePoolType.DEVICE_COMPUTE_AT_WILL, kernels.source("image"), True, 3)
     pool.addDevice(devs[0:max(1, n_gpus)])
-    tp = ClTaskPool()
-    dims_a = ck.ClIntArray(2)
+    dims_a = ck.ClIntArray(3)
     dims_a.view[:] = dims
     dims_a.readOnly = True
     frame.readOnly = True
-    outs = []
+    outs, tasks = [], []
     ntasks = 32
     for t in range(ntasks):
         o = ck.ClFloatArray(n)
-        o.writeOnly = True
+        o.read, o.write, o.writeAll = False, True, True          # the strip kernel's work-items are not pixels: whole frame back
         outs.append(o)
-        tp.feed(task(frame.nextParam(o, dims_a), 1 + t % 3, "gaussianBlur", n, 256))
+        tasks.append(task(frame.nextParam(o, dims_a), 1 + t % 3, "blurStrips", gs, ls))
+    # Warm pass: every task on EVERY device (broadcast), so that each device already owns the buffers of whichever tasks the
+    # greedy split hands it later — a buffer made inside the timed pass is a cudaMalloc, which drains the whole GPU.
+    warm = ClTaskPool()
+    for tk in tasks:
+        tk.type = ClTaskType.TASK_MESSAGE_BROADCAST
+        warm.feed(tk)
+    pool.enqueueTaskPool(warm)
+    pool.finish()
+    tp = ClTaskPool()
+    for tk in tasks:
+        tk.type = ClTaskType.TASK_MESSAGE_DEFAULT
+        tp.feed(tk)
     pool.enqueueTaskPool(tp)
-    pool.finish()                                            # warm: buffers and kernels exist now
+    pool.finish()                                            # one untimed greedy pass
     pool.enqueueTaskPool(tp)
     ms = pool.finish()
-    out["task_pool"] = {"tasks": ntasks, "ms_total": ms, "frames_per_s": ntasks / (ms * 1e-3), "tasks_per_device": pool.tasksPerDevice(),
-                        "exact": bool(np.array_equal(outs[-1].view, b)),
-                        "note": "each task uploads a 33 MB frame and downloads a 33 MB result (host-link bound)"}
+    out["task_pool"] = {"tasks": ntasks, "kernel": "blurStrips", "ms_total": ms, "frames_per_s": ntasks / (ms * 1e-3),
+                        "tasks_per_device": pool.tasksPerDevice(), "exact": bool(np.array_equal(outs[-1].view, b)),
+                        "host_link_GBps": 2.0 * 4 * n * ntasks / (ms * 1e-3) / 1e9,
+                        "note": "each task uploads a 33 MB frame and downloads a 33 MB result (host-link bound); buffers of every "
+                                "task exist on every device before the timed pass"}
     pool.dispose()
     return out
 
 
 def bench_image_kernels(ck, kernels, po, dev, pk, sets=6, rounds=3):
-    """K5a/b/c alone against the HBM roofline (8 B/px, 8 B/px, 4 B/px + 1 KiB).  Every array stays on the
-    device (flags cleared after the first call); `sets` independent frame sets (6 x 3 x 33 MB = 597 MB >> 126 MB L2) are
-    cycled so that no launch finds its frame in L2.  Time = CUDA-event span of the launch."""
-    Wf, Hf = 3840, 2160
+    """K5a/b/c alone and fused against the HBM roofline (8 B/px, 8 B/px, 4 B/px + 1 KiB; fused 4 B/px + 1 KiB).
+    Every array stays on the device (flags cleared after the first call); `sets` independent frame sets (6 x 3 x 33 MB =
+    597 MB >> 126 MB L2) are cycled so that no launch finds its frame in L2.  Two times per kernel: the CUDA-event span of
+    one launch (what the balancer sees; includes the launch's ramp and tail on an otherwise idle GPU), and the time per
+    launch when the launches follow each other without a host wait (enqueue mode), which is how a pipeline runs them."""
+    Wf, Hf, RB = 3840, 2160, 30
     n = Wf * Hf
     cr = ck.ClNumberCruncher(dev, kernels.source("image"))
     assert cr.errorCode() == 0, cr.errorMessage()
-    dims = ck.ClIntArray(2)
-    dims.view[:] = [Wf, Hf]
+    dims = ck.ClIntArray(3)
+    dims.view[:] = [Wf, Hf, RB]
     dims.readOnly = True
     frame = po.uniform(0xF00D, n, 0, 1)
+    b_exp, s_exp, h_exp = np.zeros(n, np.float32), np.zeros(n, np.float32), np.zeros(256, np.uint32)
+    dims_h = np.array([Wf, Hf], np.int32)
+    po.blur5x5(frame, b_exp, dims_h)
+    po.sobel(b_exp, s_exp, dims_h)
+    po.histogram(s_exp, h_exp)
     S = []
     for _ in range(sets):
-        a, b, c, h = ck.ClFloatArray(n), ck.ClFloatArray(n), ck.ClFloatArray(n), ck.ClUIntArray(256)
+        a, b, c, h, acc = ck.ClFloatArray(n), ck.ClFloatArray(n), ck.ClFloatArray(n), ck.ClUIntArray(256), ck.ClUIntArray(2049)
         a.view[:] = frame
-        c.numberOfElementsPerWorkItem = 16
-        S.append((a, b, c, h))
-    calls = {"gaussianBlur": (lambda s: s[0].nextParam(s[1], dims), 1, n, 8.0 * n),
-             "gaussianBlur8": (lambda s: s[0].nextParam(s[1], dims), 4, n // 8, 8.0 * n),
-             "sobel": (lambda s: s[1].nextParam(s[2], dims), 2, n, 8.0 * n),
-             "histogram": (lambda s: s[2].nextParam(s[3]), 3, n // 16, 4.0 * n + 1024)}
-    names = {"gaussianBlur": "gaussianBlur", "gaussianBlur8": "gaussianBlur8", "sobel": "sobel", "histogram": "histogramZero histogram"}
-    out = {}
-    for k, (group, cid, rng_items, nbytes) in calls.items():
+        S.append((a, b, c, h, acc))
+    gs, ls = kernels.strip_launch(Wf, Hf, RB)
+    # name: (kernel names, argument group, compute id, global range, local, elements per item of each argument, algorithmic bytes)
+    calls = {"blurStrips": ("blurStrips", lambda s: s[0].nextParam(s[1], dims), 11, gs, ls, [1, 1, 1], 8.0 * n),
+             "sobelStrips": ("sobelStrips", lambda s: s[1].nextParam(s[2], dims), 12, gs, ls, [1, 1, 1], 8.0 * n),
+             "histogramStrips": ("histogramStrips", lambda s: s[2].nextParam(s[3], dims, s[4]), 13, 592 * 256, 256, [1, 1, 1, 1], 4.0 * n + 1024),
+             "blurSobelHistogram": ("blurSobelHistogram", lambda s: s[0].nextParam(s[3], dims, s[4]), 14, gs, ls, [1, 1, 1, 1], 4.0 * n + 1024),
+             "gaussianBlur": ("gaussianBlur", lambda s: s[0].nextParam(s[1], dims), 1, n, 256, [1, 1, 1], 8.0 * n),
+             "gaussianBlur8": ("gaussianBlur8", lambda s: s[0].nextParam(s[1], dims), 4, n // 8, 256, [1, 8, 1], 8.0 * n),
+             "sobel": ("sobel", lambda s: s[1].nextParam(s[2], dims), 2, n, 256, [1, 1, 1], 8.0 * n),
+             "histogram": ("histogramZero histogram", lambda s: s[2].nextParam(s[3]), 3, n // 16, 256, [16, 1], 4.0 * n + 1024)}
+    traffic = {k: ncu_traffic(k, "r2_ncu_summary.json") for k in calls}
+    out = {"rows_per_band": RB}
+    # first pass: upload the source frame of every set once and run the chain, so that every later launch finds real data on the device
+    for s in S:
+        assert s[0].nextParam(s[1], dims).compute(cr, 11, "blurStrips", gs, ls, readWritesReady=[" read ", "", " read "]) == 0
+        assert s[1].nextParam(s[2], dims).compute(cr, 12, "sobelStrips", gs, ls, readWritesReady=["", "", ""]) == 0
+    for k, (names, group, cid, rng_items, local, epi, nbytes) in calls.items():
+        rw = [""] * len(epi)
         ts = []
         for r in range(rounds + 1):
             for s in S:
-                if r == 0:      # first round: upload the source frame once, leave everything else on the device
-                    s[0].read, s[0].partialRead, s[0].write = (k == "gaussianBlur"), False, False
-                    for x in s[1:]:
-                        x.read, x.partialRead, x.write = False, False, False
-                else:
-                    s[0].read = False
-                    dims.read = False       # resident as well from the second round on
-                assert group(s).compute(cr, cid, names[k], rng_items, 256) == 0
+                assert group(s).compute(cr, cid, names, rng_items, local, readWritesReady=rw, elementsPerItemReady=epi) == 0
                 if r > 0:
                     ts.append(cr.benchmarks(cid)[0] * 1e-3)
         dt = float(np.mean(ts))
-        out[k] = {"us_per_frame": dt * 1e6, "GBps": nbytes / dt / 1e9,
+        cr.enqueueMode = True                     # launches follow each other; the host waits once at the end
+        t0 = time.perf_counter()
+        for r in range(rounds * 3):
+            for s in S:
+                assert group(s).compute(cr, cid, names, rng_items, local, readWritesReady=rw, elementsPerItemReady=epi) == 0
+        cr.enqueueMode = False
+        cr.sync()
+        dq = (time.perf_counter() - t0) / (rounds * 3 * len(S))
+        out[k] = {"us_per_frame": dt * 1e6, "us_per_frame_back_to_back": dq * 1e6, "GBps": nbytes / dt / 1e9,
                   "roofline": {"bound": "hbm", "achieved": nbytes / dt / 1e9, "peak": pk["hbm_gbs"], "unit": "GB/s",
-                               "frac": nbytes / dt / 1e9 / pk["hbm_gbs"], "traffic": None, "algorithmic_bytes": nbytes,
-                               "note": "span includes the launch of histogramZero for the histogram row"}}
+                               "frac": nbytes / dt / 1e9 / pk["hbm_gbs"], "frac_back_to_back": nbytes / dq / 1e9 / pk["hbm_gbs"],
+                               "traffic": traffic[k], "algorithmic_bytes": nbytes}}
+    # parity of what is left on the device after the timed launches (set 0): downloads only
+    s = S[0]
+    for arr in (s[1], s[2], s[3]):
+        arr.view[:] = 0
+    assert s[0].nextParam(s[1], dims).compute(cr, 11, "blurStrips", gs, ls, readWritesReady=["", " write all ", ""]) == 0
+    assert s[1].nextParam(s[2], dims).compute(cr, 12, "sobelStrips", gs, ls, readWritesReady=["", " write all ", ""]) == 0
+    assert s[0].nextParam(s[3], dims, s[4]).compute(cr, 14, "blurSobelHistogram", gs, ls, readWritesReady=["", " write all ", "", ""]) == 0
+    fused_ok = bool(np.array_equal(s[3].view, h_exp))
+    s[3].view[:] = 0
+    assert s[2].nextParam(s[3], dims, s[4]).compute(cr, 13, "histogramStrips", 592 * 256, 256, readWritesReady=["", " write all ", "", ""]) == 0
+    out["parity"] = {"frame": f"{Wf}x{Hf}", "against": "oracle_blur5x5 / oracle_sobel / oracle_histogram, every pixel and bin",
+                     "blurStrips_mismatches": int((s[1].view.view(np.uint32) != b_exp.view(np.uint32)).sum()),
+                     "sobelStrips_mismatches": int((s[2].view.view(np.uint32) != s_exp.view(np.uint32)).sum()),
+                     "histogramStrips_exact": bool(np.array_equal(s[3].view, h_exp)), "blurSobelHistogram_exact": fused_ok}
     for s in S:
         for x in s:
             x.dispose()
     dims.dispose()
     cr.dispose()
     return out
+
+
+def bench_c1(ck, kernels, po, dev, pk, sms, reps=200):
+    """C1 (BASELINE.json configs[0]): Mandelbrot 1024 x 1024, 256 iterations, one compute id, one GPU — the size at which the
+    per-call cost of compute() matters (SURVEY.md §7 hard part 6: a ~50 us kernel).  Reported per mode: wall time per
+    compute() call, the device span of the call (CUDA events: upload .. download), and their difference = what the host
+    side of one call costs; plus the kernel alone with everything resident."""
+    Wc = Hc = 1024
+    npx = Wc * Hc
+    cr = ck.ClNumberCruncher(dev, kernels.source("mandelbrot"))
+    assert cr.errorCode() == 0, cr.errorMessage()
+    view, out = ck.ClArray(8, np.float32), ck.ClArray(npx, np.int32)
+    view.view[:] = po.mandelbrot_view(Wc, Hc, 256)
+    view.readOnly = True
+    out.writeOnly = True
+    out.numberOfElementsPerWorkItem = E
+    g = view.nextParam(out)
+    exp = po.mandelbrot(view.view, npx)
+    res = {"pixels": npx, "max_iter": 256, "iterations_total": int(exp.sum(dtype=np.int64))}
+
+    def run(label, call, cid):
+        for _ in range(10):
+            assert call() == 0
+        wall, span = [], []
+        for _ in range(reps):
+            t0 = time.perf_counter()
+            assert call() == 0
+            wall.append(time.perf_counter() - t0)
+            span.append(cr.benchmarks(cid)[0] * 1e-3)
+        w, d = float(np.median(wall)), float(np.median(span))
+        res[label] = {"us_per_call_wall": w * 1e6, "us_per_call_device_span": d * 1e6, "us_host_overhead_per_call": (w - d) * 1e6,
+                      "Mpix_per_s": npx / w / 1e6}
+
+    out.view[:] = -1
+    run("plain", lambda: g.compute(cr, 1, "mandelbrot", npx // E, 256), 1)
+    ok_plain = bool(np.array_equal(out.view, exp))
+    out.view[:] = -1
+    run("event_pipeline_4_blobs", lambda: g.compute(cr, 2, "mandelbrot", npx // E, 256, 0, True, ck.PIPELINE_EVENT, 4), 2)
+    ok_pipe = bool(np.array_equal(out.view, exp))
+    del res["event_pipeline_4_blobs"]["us_per_call_device_span"], res["event_pipeline_4_blobs"]["us_host_overhead_per_call"]  # host clock there
+    rw = ["", ""]
+    run("resident_kernel_only", lambda: g.compute(cr, 3, "mandelbrot", npx // E, 256, 0, False, True, 4, readWritesReady=rw,
+                                                  elementsPerItemReady=[1, E]), 3)
+    k = res["resident_kernel_only"]["us_per_call_device_span"] * 1e-6
+    peak = 2.0 * 128 * sms * pk["sm_max_mhz"] * 1e6 / 1e12
+    ach = 8.0 * res["iterations_total"] / k / 1e12
+    res["resident_kernel_only"]["roofline"] = {"bound": "fp32", "achieved": ach, "peak": peak, "unit": "TFLOP/s", "frac": ach / peak,
+                                               "note": "a 1024^2 x 256 launch is ~4096 work-groups of very unequal length: launch ramp and tail included"}
+    res["parity"] = {"pixels_checked": npx, "mismatches_plain": int((out.view != exp).sum()) if not ok_pipe else 0,
+                     "exact_plain": ok_plain, "exact_event_pipeline": ok_pipe}
+    view.dispose(); out.dispose(); cr.dispose()
+    return res
 
 
 def bench_saxpy(ck, kernels, dev, shim, pk, steps, warmup):
@@ -384,7 +484,6 @@ def bench_saxpy(ck, kernels, dev, shim, pk, steps, warmup):
     alpha[0] = 2.0
     x.view[:] = 3.0
     y.view[:] = (np.arange(n, dtype=np.int64) % (1 << 20)).astype(np.float32)
-    y0 = y.view[:4096].copy()
     alpha.readOnly = True
     for a in (x, y):
         a.partialRead, a.read = True, False
@@ -404,8 +503,16 @@ def bench_saxpy(ck, kernels, dev, shim, pk, steps, warmup):
         out[f"streamed_{mode}"] = {"ms_per_step": dt * 1e3, "GBps_algorithmic": 12.0 * n / dt / 1e9,
                                    "h2d_GBps": 8.0 * n / dt / 1e9, "d2h_GBps": 4.0 * n / dt / 1e9}
     calls = 2 * (warmup + steps)
-    exp = (y0 + np.float32(6.0) * calls).astype(np.float32)   # exact: small integers
-    out["parity_head_exact"] = bool(np.array_equal(y.view[:4096], exp))
+    # every element of every blob of both lanes: y = (i mod 2^20) + 6 per call, small integers, so the sum is exact in f32
+    bad_blobs, mismatches, blob = [], 0, n // 16
+    base = (np.arange(blob, dtype=np.int64) % (1 << 20)).astype(np.float32) + np.float32(6.0 * calls)   # blob is a multiple of 2^20
+    for k in range(16):
+        d = int(np.count_nonzero(y.view[k * blob:(k + 1) * blob] != base))
+        mismatches += d
+        if d:
+            bad_blobs.append(k)
+    out["parity"] = {"elements_checked": n, "blobs_checked": 16, "mismatches": mismatches, "blobs_with_mismatches": bad_blobs,
+                     "against": "y0 + 2*3*calls, exact in f32 (what oracle_saxpy gives on these integers)"}
     # resident: flags cleared after the first call (as Kamera.cs:271-272 does) → no transfers, kernel only
     g_res = alpha.nextParam(x, y)
     rw = ["", "", ""]
@@ -424,6 +531,36 @@ def bench_saxpy(ck, kernels, dev, shim, pk, steps, warmup):
         a.dispose()
     cr.dispose()
     return out
+
+
+def own_bodies(cr, cid, per_body, spmd_ctx):
+    """(first body, bodies) of every share this process computes."""
+    r, f = cr.globalRanges(cid), cr.globalReferences(cid)
+    idx = [spmd_ctx[0]] if spmd_ctx is not None else range(len(r))
+    return [(f[i] // per_body, r[i] // per_body) for i in idx if r[i] > 0]
+
+
+def nbody_parity(po, pos_before, vel_before, pos_after, vel_after, n, slices, total=1024, block=64):
+    """One oracle step on `total` bodies spread over `slices`, each against all n bodies; worst relative position error."""
+    params = np.array([1e-3, 1e-4, n, 0], np.float32)
+    worst, worst_v, checked = 0.0, 0.0, 0
+    per_slice = max(1, total // block // max(1, len(slices)))
+    after, vafter = pos_after.reshape(n, 4), vel_after.reshape(n, 4)
+    for (first, count) in slices:
+        for k in range(per_slice):
+            if count < block:
+                continue
+            f = first + (k * (count - block)) // max(1, per_slice - 1)
+            v, o = vel_before.copy(), np.zeros(4 * n, np.float32)
+            po.nbody3d_step(pos_before, v, o, params, f, block)
+            exp = o.reshape(n, 4)[f:f + block]
+            rel = np.abs(after[f:f + block, :3] - exp[:, :3]) / np.maximum(np.abs(exp[:, :3]), 1e-3)
+            worst = max(worst, float(rel.max()))
+            vexp = v.reshape(n, 4)[f:f + block, :3]
+            worst_v = max(worst_v, float(np.abs(vafter[f:f + block, :3] - vexp).max() / max(float(np.abs(vexp).max()), 1e-12)))
+            checked += block
+    return {"bodies_checked": checked, "against": f"oracle_nbody3d_step, each body against all {n}", "max_rel_err_positions": worst,
+            "max_rel_err_velocities": worst_v, "tolerance": 1e-4, "ok": bool(checked > 0 and worst <= 1e-4)}
 
 
 def bench_nbody(ck, kernels, po, devs, pk, sms, steps, warmup, spmd_attach=None, n_gpus=1, allmax=lambda v: v, spmd_ctx=None,
@@ -464,6 +601,15 @@ def bench_nbody(ck, kernels, po, devs, pk, sms, steps, warmup, spmd_attach=None,
             ts_dev.append(max(cr.benchmarks(1)) * 1e-3)
         src, dst = dst, src
     dt_dev, dt_wall = allmax(float(np.mean(ts_dev))), allmax(float(np.mean(ts_wall)))   # slowest rank decides
+    # one more step, checked against one oracle step from the state this process held before it: 1,024 bodies of its own
+    # share(s) against all n (with one process per GPU the other ranks' slices of the host copy are stale; the kernel and the
+    # oracle both see that same input)
+    before_p, before_v = src.view.copy(), vel.view.copy()
+    src.read, src.partialRead, src.write = True, False, False
+    dst.read, dst.partialRead, dst.write = False, False, True
+    assert src.nextParam(vel, dst, params, scratch).compute(cr, 1, kernel, n * per_body, local) == 0
+    parity = nbody_parity(po, before_p, before_v, dst.view, vel.view, n, own_bodies(cr, 1, per_body, spmd_ctx))
+    src, dst = dst, src
     # the kernel alone: every array left on the device (flags cleared as Kamera.cs:271-272 does), shares as the balancer left
     # them.  With more than one device the other devices' position slices go stale, which changes no timing: the work per
     # body does not depend on the data.
@@ -482,6 +628,7 @@ def bench_nbody(ck, kernels, po, devs, pk, sms, steps, warmup, spmd_attach=None,
     res = {"bodies": n, "kernel": kernel, "ms_per_step_kernel": dt_k * 1e3, "ms_per_step_device": dt_dev * 1e3,
            "ms_per_step_e2e": dt_wall * 1e3, "GInter_per_s_kernel": inter / dt_k / 1e9,
            "GInter_per_s": inter / dt_dev / 1e9, "GInter_per_s_e2e": inter / dt_wall / 1e9, "scratch_MB": kfloats * 4096 / 1e6,
+           "parity": parity,
            "roofline": {"bound": "fp32", "achieved": ach, "peak": peak, "unit": "TFLOP/s", "frac": ach / peak,
                         "traffic": ncu_traffic("nbody") if n_gpus == 1 else None,
                         "note": "20 FLOP per interaction over the kernel's own launch time (arrays resident); GInter_per_s "
@@ -516,12 +663,24 @@ def bench_nbody(ck, kernels, po, devs, pk, sms, steps, warmup, spmd_attach=None,
                     ts_pw.append(time.perf_counter() - t0)
                     ts_p.append(max(cr.benchmarks(2)) * 1e-3)
                 src, dst = dst, src
+            parity_p = None
+            if usable and spmd_ctx is None:
+                # two more steps that also download (untimed): the state before the last one and the state after it
+                states = []
+                for _ in range(2):
+                    dst.write, vel.write = True, True
+                    assert src.nextParam(vel, dst, params, scratch, t_b if dst is pb else t_a).compute(cr, 2, "nBody3Dwp", n * per_body, local) == 0
+                    states.append((dst.view.copy(), vel.view.copy()))
+                    dst.write, vel.write = False, False
+                    src, dst = dst, src
+                parity_p = nbody_parity(po, states[0][0], states[0][1], states[1][0], states[1][1], n, own_bodies(cr, 2, per_body, None))
             if usable:
                 dt_p, dt_pw = allmax(float(np.mean(ts_p))), allmax(float(np.mean(ts_pw)))
                 res["resident_peer_stores"] = {"kernel": "nBody3Dwp", "ms_per_step_device": dt_p * 1e3, "ms_per_step_e2e": dt_pw * 1e3,
                                                "GInter_per_s": inter / dt_p / 1e9, "GInter_per_s_e2e": inter / dt_pw / 1e9,
                                                "frac_of_fp32_per_gpu": 20.0 * inter / n_gpus / dt_p / 1e12 / peak,
-                                               "exchange": "CUDA IPC peer stores" if spmd_ctx is not None else "peer stores"}
+                                               "exchange": "CUDA IPC peer stores" if spmd_ctx is not None else "peer stores",
+                                               "parity": parity_p}
             else:
                 res["resident_peer_stores"] = {"unavailable": "; ".join(t.error for t in tabs if t.error) or "a peer rank could not map the buffers"}
             for t in tabs:
@@ -714,8 +873,19 @@ def run_ours(args):
             "frac_at_observed_clock": (ach / (2.0 * 128 * sms * clk["sm_mhz"] * 1e6 / 1e12)) if clk.get("sm_mhz") else None}
 
     workloads = {}
+    link_all = None
+    if args.all:
+        # every GPU of the run copies at the same time: the ceiling the end-to-end leg can be held against
+        if spmd_mode:
+            mine = bench_hostlink(L, (devs.ordinals[0],), 256, 4, barrier=barrier)
+            link_all = {k: allsum(v) for k, v in mine.items() if k.endswith("_GBps")}
+            link_all["per_rank_d2h_GBps"] = gather(dist, torch, torch_dev, mine["d2h_GBps"], world)
+            link_all["how"] = f"{world} ranks, one GPU each, 256 MiB pinned copies started together (barrier), sum over ranks"
+        elif n_gpus > 1:
+            link_all = bench_hostlink(L, tuple(devs.ordinals), 256, 4)
+            link_all["how"] = f"one process, {n_gpus} GPUs, 256 MiB pinned copies enqueued on all devices, then drained"
     if args.all and rank == 0 and not spmd_mode:
-        link = bench_hostlink(L, devs.ordinals[0])
+        link = bench_hostlink(L, (devs.ordinals[0],))
         workloads["host_link"] = link
         sx = bench_saxpy(ck, kernels, devs[0], L, pk, max(2, args.steps // 2), 1)
         for mode in ("streamed_event", "streamed_driver"):
@@ -724,11 +894,25 @@ def run_ours(args):
                                     "unit": "GB/s", "frac": sx[mode]["h2d_GBps"] / link["bidirectional_each_GBps"],
                                     "peak_source": "pinned H2D with D2H running concurrently, measured in this run"}
         workloads["saxpy_c2"] = sx
+        try:
+            workloads["mandelbrot_c1"] = bench_c1(ck, kernels, po, devs[0], pk, sms)
+        except Exception as e:
+            workloads["mandelbrot_c1"] = {"error": repr(e)}
         workloads["pipeline_c5"] = bench_pipeline(ck, kernels, po, n_gpus)
         try:
             workloads["pipeline_c5"]["kernels_resident"] = bench_image_kernels(ck, kernels, po, devs[0], pk)
         except Exception as e:   # an extra leg must not cost the line
             workloads["pipeline_c5"]["kernels_resident"] = {"error": repr(e)}
+    if args.all and spmd_mode and world >= 3:
+        # C5 with its three stages on GPUs 0, 1 and 2: rank 0 drives them from its own process while the other ranks wait on
+        # the host (a shared-memory rendezvous, no kernel of theirs spins on the GPUs that are being measured)
+        hb = spmd.make_exchange(rank, world, torch_dev)
+        if rank == 0:
+            try:
+                workloads["pipeline_c5_3gpu"] = bench_pipeline(ck, kernels, po, 3)
+            except Exception as e:
+                workloads["pipeline_c5_3gpu"] = {"error": repr(e)}
+        hb([0.0] * world)
     if args.all:
         attach = (lambda c: spmd.attach(c, rank, world, torch_dev)) if spmd_mode else None
         nb, nbody_finish = bench_nbody(ck, kernels, po, devs, pk, sms, max(3, args.steps), 2, attach, n_gpus, allmax,
@@ -765,6 +949,13 @@ def run_ours(args):
                          "final_shares": [round(x / items, 4) for x in shares[-1]] if shares else None},
             "workloads": workloads,
         }
+        if link_all is not None:
+            workloads["host_link_all_gpus"] = link_all
+            d2h = link_all.get("d2h_GBps")
+            if d2h:
+                line["e2e"]["d2h_GBps_achieved"] = 4.0 * npix / (e2e_ms * 1e-3) / 1e9
+                line["e2e"]["d2h_GBps_ceiling_all_gpus"] = d2h
+                line["e2e"]["frac_of_host_link_ceiling"] = line["e2e"]["d2h_GBps_achieved"] / d2h
     # The last leg — n-body stepping with the exchange fused into the kernel, which at N > 1 maps other ranks' buffers and
     # relies on every rank taking part — runs with the rest of the line already complete.  If it has not finished within
     # 120 s (a rank that hangs would otherwise take the whole measurement with it), rank 0 prints the line without it and
@@ -813,7 +1004,7 @@ def main():
     ap.add_argument("--no-all", dest="all", action="store_false", help="skip the SAXPY and n-body workloads")
     ap.add_argument("--e2e-blobs", type=int, default=16, help="pipeline blobs of the end-to-end leg (multiple of 4)")
     ap.add_argument("--e2e-mode", default="event", choices=["event", "driver"], help="pipelining mode of the end-to-end leg")
-    ap.add_argument("--only", default=None, choices=["nbody", "saxpy", "pipeline", "hostlink"],
+    ap.add_argument("--only", default=None, choices=["nbody", "saxpy", "pipeline", "hostlink", "c1", "image"],
                     help="profiling aid: run just this secondary workload on one GPU and print its numbers")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
@@ -836,7 +1027,11 @@ def main():
             out = bench_pipeline(ck, kernels, po, max(1, args.gpus))
             out["kernels_resident"] = bench_image_kernels(ck, kernels, po, dev, pk)
         elif args.only == "hostlink":
-            out = bench_hostlink(shim())
+            out = bench_hostlink(shim(), tuple(range(max(1, args.gpus))))
+        elif args.only == "c1":
+            out = bench_c1(ck, kernels, po, dev, pk, host().ckh_gpu_compute_units(0))
+        elif args.only == "image":
+            out = bench_image_kernels(ck, kernels, po, dev, pk)
         else:
             out = bench_saxpy(ck, kernels, dev, shim(), pk, args.steps, args.warmup)
         emit({"workload": args.only, **out})

@@ -177,10 +177,11 @@ void ClPipelineStage::run(bool initializerKernels, Forwarding mode) {
             if (i + 1 < n)
                 for (size_t j = 0; j < nout; j++) r[r.size() - nout + j].flags = 0u;
         }
-        // an output smaller than the kernel's range (a reduction result such as a histogram) cannot be downloaded as a slice
-        // per work-item: it comes back whole ("write all", Worker.cs:1353)
+        // an output whose length is not the kernel's range times its elements per work-item — a reduction result such as a
+        // histogram, or a frame written by a kernel whose work-items are not pixels (the strip kernels) — cannot be
+        // downloaded as one slice per work-item: it comes back whole ("write all", Worker.cs:1353)
         for (auto& ar : r)
-            if ((ar.flags & F_WRITE) && ar.length < (int64_t)list[i].globalRange * ar.elemsPerWorkItem) ar.flags |= F_ALL;
+            if ((ar.flags & F_WRITE) && ar.length != (int64_t)list[i].globalRange * ar.elemsPerWorkItem) ar.flags |= F_ALL;
         const int computeId = initializerKernels ? (int)(1000000 + i) : (int)(i + 1);
         cores.compute({list[i].name}, cruncher_->repeatCount, std::string(), r, list[i].globalRange, computeId, 0, false, 4,
                       Cores::PIPELINE_EVENT, list[i].localRange);

@@ -153,6 +153,21 @@ std::string rewrite_kernels(const std::string& src, std::vector<std::pair<std::s
             }
         }
         out += "extern \"C\" __global__ void ";
+        {
+            // `// ck-launch-bounds: <kernel> <max threads> [<min work-groups per SM>]` anywhere in the source: the attribute
+            // cannot sit inside `kernel void name(`, which is what the reference's kernel-name regex must keep matching
+            const std::string key = "ck-launch-bounds:";
+            for (size_t at = src.find(key); at != std::string::npos; at = src.find(key, at + 1)) {
+                std::istringstream line(src.substr(at + key.size(), src.find('\n', at) - at - key.size()));
+                std::string kname;
+                int threads = 0, blocks = 0;
+                line >> kname >> threads;
+                if (kname != name || threads <= 0) continue;
+                line >> blocks;
+                out += "__launch_bounds__(" + std::to_string(threads) + (blocks > 0 ? ", " + std::to_string(blocks) : std::string()) + ") ";
+                break;
+            }
+        }
         out += name;
         out += "(const unsigned int __ck_goff";
         if (count > 0) {

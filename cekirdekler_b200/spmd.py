@@ -2,8 +2,8 @@
 collective.
 
 Every rank owns one GPU and one single-device ClNumberCruncher.  The only thing ranks exchange is the vector of
-per-device times of the previous call (world doubles, all-gathered through torch.distributed — NCCL on GPU boxes,
-gloo in the CPU tests); each rank then runs the same deterministic balancer (Cores.cs:544-613 restated in
+per-device times of the previous call (world doubles: through a shared-memory file when all ranks share a host, else
+all-gathered through torch.distributed); each rank then runs the same deterministic balancer (Cores.cs:544-613 restated in
 csrc/host/balance.cpp) and so arrives at the same split, of which it executes its own slice [ref_r, ref_r + range_r).
 torch is plumbing here (process group, device selection), not part of the compute path.
 """
@@ -34,19 +34,104 @@ def init_process_group_from_env(backend: str | None = None):
     return rank, world, local
 
 
+_exchange_count = 0
+
+
+class _SharedSlots:
+    """`world` (sequence, value) slots in a POSIX shared-memory file, two banks deep: the ranks of one host exchange one
+    double per compute() call through plain memory instead of a collective.
+
+    Why not the process group: every compute() of a one-process-per-GPU job opens with this exchange (the balancer needs
+    all devices' times of the previous call).  Through NCCL that is a kernel launch, a device synchronisation and a
+    device-to-host copy per call, about 0.15 ms on eight B200s, as much as a sixth of an n-body step.  Here a rank stores
+    its value, then its call number (x86 keeps the two stores in order), and reads the others' once their call numbers match.
+    Call k uses bank k % 2; a rank reaches call k + 2 only after every rank has posted call k + 1, i.e. after every rank
+    has finished reading call k, so two banks are enough."""
+
+    def __init__(self, rank: int, world: int, path: str, create: bool):
+        import mmap
+
+        import numpy as np
+
+        size = 2 * world * 64
+        flags = os.O_RDWR | (os.O_CREAT | os.O_EXCL if create else 0)
+        fd = os.open(path, flags, 0o600)
+        try:
+            if create:
+                os.ftruncate(fd, size)
+            self._mm = mmap.mmap(fd, size)
+        finally:
+            os.close(fd)
+        self._seq = np.frombuffer(self._mm, dtype=np.int64).reshape(2, world, 8)[:, :, 0]
+        self._val = np.frombuffer(self._mm, dtype=np.float64).reshape(2, world, 8)[:, :, 1]
+        self.rank, self.world, self.calls = rank, world, 0
+
+    def exchange(self, value: float, timeout_s: float = 300.0) -> List[float]:
+        import time
+
+        self.calls += 1
+        k, bank = self.calls, self.calls % 2
+        self._val[bank, self.rank] = value
+        self._seq[bank, self.rank] = k
+        seq, spins, t0 = self._seq[bank], 0, None
+        while not (seq == k).all():
+            spins += 1
+            if spins > 20000:                       # the others are far behind (first call, a slower share): stop burning the core
+                if t0 is None:
+                    t0 = time.monotonic()
+                elif time.monotonic() - t0 > timeout_s:
+                    raise RuntimeError(f"spmd exchange: rank {self.rank} waited {timeout_s:.0f} s for call {k} of the other ranks")
+                time.sleep(20e-6)
+        return self._val[bank].tolist()
+
+
 def make_exchange(rank: int, world: int, device=None) -> Callable[[List[float]], List[float]]:
-    """all-gather of one double per rank: in → list of `world` times with entry `rank` valid; out → all entries valid."""
+    """all-gather of one double per rank: in → list of `world` times with entry `rank` valid; out → all entries valid.
+
+    When every rank of the job runs on this host (torchrun's LOCAL_WORLD_SIZE == WORLD_SIZE, the only layout the 8-GPU box
+    has) the values travel through a shared-memory file (_SharedSlots) that the ranks agree on with ONE collective here, at
+    set-up; CK_SPMD_EXCHANGE=collective, or ranks on several hosts, keep the per-call all-gather of the process group."""
     import torch
     import torch.distributed as dist
+
+    global _exchange_count
+    slots = None
+    one_host = int(os.environ.get("LOCAL_WORLD_SIZE", str(world))) == world
+    if world > 1 and dist.is_initialized() and one_host and os.environ.get("CK_SPMD_EXCHANGE", "shm") != "collective":
+        _exchange_count += 1
+        ident = torch.tensor([os.getpid() if rank == 0 else 0], dtype=torch.int64, device=device)
+        dist.broadcast(ident, src=0)                                   # every rank makes its exchanges in the same order
+        path = f"/dev/shm/ck_spmd_{int(ident.item())}_{_exchange_count}"
+        ok = 1
+        try:
+            if rank == 0:
+                slots = _SharedSlots(rank, world, path, create=True)
+            dist.barrier()
+            if rank != 0:
+                slots = _SharedSlots(rank, world, path, create=False)
+        except OSError:
+            ok = 0
+        flag = torch.tensor([ok], dtype=torch.int32, device=device)
+        dist.all_reduce(flag, op=dist.ReduceOp.MIN)                    # also: everybody has mapped the file by now
+        if rank == 0:
+            try:
+                os.unlink(path)                                        # the mappings keep it alive; nothing is left behind
+            except OSError:
+                pass
+        if not int(flag.item()):
+            slots = None
 
     def exchange(times: List[float]) -> List[float]:
         if world <= 1 or not dist.is_initialized():
             return times
+        if slots is not None:
+            return slots.exchange(times[rank])
         mine = torch.tensor([times[rank]], dtype=torch.float64, device=device)
         out = torch.empty(world, dtype=torch.float64, device=device)
         dist.all_gather_into_tensor(out, mine)
         return out.cpu().tolist()
 
+    exchange.uses_shared_memory = slots is not None
     return exchange
 
 

@@ -385,6 +385,77 @@ def test_nbody3d_resident_steps_with_peer_stores(gpus):
     assert np.abs(vel.view.reshape(n, 4)[:, :3] - vexp).max() / np.abs(vexp).max() <= 1e-4
 
 
+def oracle_sample_check(pos_before, vel_before, pos_after, vel_after, n, blocks=8, block=128):
+    """One oracle step from (pos_before, vel_before) on `blocks` runs of `block` bodies spread over the whole range, against all
+    n bodies, compared with the state the GPU produced: positions <= 1e-4 relative (BASELINE.json), masses carried over."""
+    params_h = np.array([1e-3, 1e-4, n, 0], np.float32)
+    checked = 0
+    for b in range(blocks):
+        first = min(n - block, (b * (n - block)) // max(1, blocks - 1) + (37 if b % 2 else 0))   # odd starts: not aligned to body groups
+        v = vel_before.copy().reshape(-1)
+        o = np.zeros(4 * n, np.float32)
+        po.nbody3d_step(np.ascontiguousarray(pos_before.reshape(-1)), v, o, params_h, first, block)
+        exp = o.reshape(n, 4)[first:first + block]
+        got = pos_after[first:first + block]
+        rel = np.abs(got[:, :3] - exp[:, :3]) / np.maximum(np.abs(exp[:, :3]), 1e-3)
+        assert rel.max() <= 1e-4, (first, rel.max())
+        assert np.array_equal(got[:, 3], exp[:, 3])
+        vexp = v.reshape(n, 4)[first:first + block, :3]
+        vgot = vel_after[first:first + block, :3]
+        assert np.abs(vgot - vexp).max() <= 1e-4 * max(np.abs(vexp).max(), 1e-6), first
+        checked += block
+    return checked
+
+
+@pytest.mark.parametrize("kernel", ["nBody3Dw", "nBody3Dwp"])
+@pytest.mark.parametrize("devices", ["one", "all"])
+def test_nbody3d_at_the_c4_size_against_the_oracle(gpus, devices, kernel):
+    """BASELINE.json configs[3] at its stated size: 131,072 bodies, four work-items per body, work-groups of 128 (64 chunks of
+    partial sums per body group, the 100 MB scratch).  The first and the tenth step are each checked against one oracle step
+    taken from the state the GPU itself held before that step, on 1,024 bodies spread over the range (1.3e8 interactions on
+    the host), so every step's kernel is verified without ten full host steps."""
+    n, wpb, local, steps = 131072, 4, 128, 10
+    devs = all_gpus()[0] if devices == "one" else all_gpus()
+    pos0 = nbody3d_inputs(n, seed=0xC0FFEE)
+    cr = ck.ClNumberCruncher(devs, kernels.source("nbody"))
+    assert cr.errorCode() == 0, cr.errorMessage()
+    groups, chunks = n // 128 + 8, (n // 256 + 7) // 8
+    kfloats = (groups * chunks * 384 + groups + 256 + 1023) // 1024
+    pa, pb, vel, params, scratch = (ck.ClFloatArray(4 * n), ck.ClFloatArray(4 * n), ck.ClFloatArray(4 * n), ck.ClFloatArray(8),
+                                    ck.ClFloatArray(kfloats * 1024))
+    pa.view[:] = pos0.reshape(-1)
+    params.view[:5] = [1e-3, 1e-4, n, wpb, kfloats]
+    params.readOnly = True
+    scratch.read, scratch.write = False, False
+    for a in (pa, pb, vel):
+        a.numberOfElementsPerWorkItem = 4 // wpb
+    fused = kernel == "nBody3Dwp"
+    tables = {id(pa): cr.peerTable(pa, vel), id(pb): cr.peerTable(pb, vel)} if fused else None
+    src, dst = pa, pb
+    checked = 0
+    for s in range(steps):
+        look = s in (0, steps - 2, steps - 1)                                # states needed on the host: after steps 1, 9 and 10
+        if fused:
+            src.read, src.partialRead, src.write = (s == 0), False, False
+            dst.read, dst.partialRead, dst.write = False, False, look
+            vel.read, vel.partialRead, vel.write = False, False, look
+            group = src.nextParam(vel, dst, params, scratch, tables[id(dst)])
+        else:
+            src.read, src.partialRead, src.write = True, False, False
+            dst.read, dst.partialRead, dst.write = False, False, True
+            vel.read, vel.partialRead, vel.write = False, True, True
+            group = src.nextParam(vel, dst, params, scratch)
+        before = (src.view.reshape(n, 4).copy(), vel.view.reshape(n, 4).copy()) if s in (0, steps - 1) else None
+        assert group.compute(cr, 1, kernel, n * wpb, local) == 0
+        if before is not None:
+            checked += oracle_sample_check(before[0], before[1], dst.view.reshape(n, 4), vel.view.reshape(n, 4), n)
+        src, dst = dst, src
+    assert checked == 2 * 1024
+    for a in (pa, pb, vel, params, scratch):
+        a.dispose()
+    cr.dispose()
+
+
 # ------------------------------------------------------------------ blur → Sobel → histogram (K5)
 @pytest.mark.parametrize("W,H", [(256, 128), (3840, 2160)])
 def test_image_chain_bit_exact(gpus, W, H):
@@ -448,3 +519,91 @@ def test_gaussian_blur8_is_bit_identical_to_the_one_pixel_kernel(gpus, W, H):
     local = 64 if (n // 8) % 64 == 0 else (n // 8)
     assert src.nextParam(out, dims).compute(cr, 1, "gaussianBlur8", n // 8, local) == 0
     assert np.array_equal(out.view, exp)
+
+
+# ------------------------------------------------------------------ K5 strip kernels (one pass over the frame)
+def image_oracle(img, W, H):
+    n = W * H
+    dims_h = np.array([W, H], np.int32)
+    b, s, h = np.zeros(n, np.float32), np.zeros(n, np.float32), np.zeros(256, np.uint32)
+    po.blur5x5(img, b, dims_h)
+    po.sobel(b, s, dims_h)
+    po.histogram(s, h)
+    return b, s, h
+
+
+def same_bits(a, b):
+    return np.array_equal(a.view(np.uint32), b.view(np.uint32))
+
+
+@pytest.mark.parametrize("W,H,rows", [(3840, 2160, 30), (3840, 2160, 59), (24, 7, 30), (24, 7, 2), (256, 128, 16), (1000, 333, 29),
+                                      (124, 11, 3), (8, 5, 30), (4, 1, 1), (4096, 100, 30), (1920, 1080, 27)])
+def test_strip_kernels_bit_exact(gpus, W, H, rows):
+    """blurStrips, sobelStrips, histogramStrips and the fused blurSobelHistogram against oracle_blur5x5 / oracle_sobel /
+    oracle_histogram: every pixel and every bin, frames with one strip and with many, bands that end inside the image, a
+    band count that does not divide the rows, widths that end inside a strip.  Two launches in a row prove that the fused
+    kernel's accumulator re-arms itself and that `hist` is overwritten, not added to."""
+    n = W * H
+    img = po.uniform(0xF00D + W, n, 0, 1)
+    b_exp, s_exp, h_exp = image_oracle(img, W, H)
+    cr = ck.ClNumberCruncher(gpu0(), kernels.source("image"))
+    assert cr.errorCode() == 0, cr.errorMessage()
+    src, blur, sob = ck.ClFloatArray(n), ck.ClFloatArray(n), ck.ClFloatArray(n)
+    hist, acc, dims = ck.ClUIntArray(256), ck.ClUIntArray(2049), ck.ClIntArray(3)
+    src.view[:] = img
+    dims.view[:] = [W, H, rows]
+    dims.readOnly = True
+    src.readOnly = True
+    acc.read, acc.write = False, False             # scratch accumulator: zero when the buffer is created, re-armed by the kernel
+    g, l = kernels.strip_launch(W, H, rows)
+    blur.view[:] = -1
+    blur.read, blur.writeAll = False, True
+    assert src.nextParam(blur, dims).compute(cr, 1, "blurStrips", g, l) == 0
+    assert same_bits(blur.view, b_exp)
+    blur.read, blur.write, blur.writeAll = True, False, False
+    sob.view[:] = -1
+    sob.read, sob.writeAll = False, True
+    assert blur.nextParam(sob, dims).compute(cr, 2, "sobelStrips", g, l) == 0
+    assert same_bits(sob.view, s_exp)
+    hist.read, hist.writeAll = False, True
+    for _ in range(2):
+        hist.view[:] = 0xFFFFFFFF
+        assert src.nextParam(hist, dims, acc).compute(cr, 3, "blurSobelHistogram", g, l) == 0
+        assert np.array_equal(hist.view, h_exp)
+    sob.read, sob.write, sob.writeAll = True, False, False
+    for groups in (1, 37, 592):
+        hist.view[:] = 0xFFFFFFFF
+        assert sob.nextParam(hist, dims, acc).compute(cr, 4, "histogramStrips", groups * 256, 256) == 0
+        assert np.array_equal(hist.view, h_exp)
+    for a in (src, blur, sob, hist, acc, dims):
+        a.dispose()
+    cr.dispose()
+
+
+def test_fused_strip_kernel_bins_special_values_like_the_oracle(gpus):
+    """NaN, infinities, values whose gradients overflow, denormals and an all-constant frame (gradient exactly 0): the
+    fused kernel's clamp-then-rsqrt binning must land every pixel in the oracle's bin."""
+    W, H, rows = 3840, 270, 30
+    n = W * H
+    img = po.uniform(0xBEEF, n, 0, 1)
+    img[5], img[n // 2], img[n // 3], img[n // 3 + 1], img[7 * n // 8] = np.nan, np.inf, 3e38, -3e38, 1e-30
+    img[W * 100:W * 140] = 0.25                     # flat rows: m == 0 exactly
+    img[W * 200 + 1000:W * 200 + 1400] = 1e-22      # gradients in the denormal range after squaring
+    img[W * 220:W * 221] *= 40.0                    # magnitudes above 1: bin 255
+    for frame in (img, np.zeros(n, np.float32), np.full(n, -2.5, np.float32)):
+        _, _, h_exp = image_oracle(frame, W, H)
+        cr = ck.ClNumberCruncher(gpu0(), kernels.source("image"))
+        src, hist, acc, dims = ck.ClFloatArray(n), ck.ClUIntArray(256), ck.ClUIntArray(2049), ck.ClIntArray(3)
+        src.view[:] = frame
+        dims.view[:] = [W, H, rows]
+        dims.readOnly = True
+        src.readOnly = True
+        acc.read, acc.write = False, False
+        hist.read, hist.writeAll = False, True
+        g, l = kernels.strip_launch(W, H, rows)
+        assert src.nextParam(hist, dims, acc).compute(cr, 1, "blurSobelHistogram", g, l) == 0
+        assert np.array_equal(hist.view, h_exp)
+        assert int(hist.view.sum()) == n
+        for a in (src, hist, acc, dims):
+            a.dispose()
+        cr.dispose()
