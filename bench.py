@@ -48,7 +48,8 @@ METRIC = "mandelbrot_mpix_per_s"
 UNIT = "Mpix/s"
 W = H = 16384
 MAX_ITER = 4096
-E = 4  # pixels per work-item of the `mandelbrot` kernel
+E = 1  # pixels per work-item: 1 for `mandelbrot1` (the default), 4 for `mandelbrot`; set from --mandel-kernel in main()
+MK = "mandelbrot1"
 
 
 def peaks():
@@ -455,14 +456,14 @@ def bench_c1(ck, kernels, po, dev, pk, sms, reps=200):
                       "Mpix_per_s": npx / w / 1e6}
 
     out.view[:] = -1
-    run("plain", lambda: g.compute(cr, 1, "mandelbrot", npx // E, 256), 1)
+    run("plain", lambda: g.compute(cr, 1, MK, npx // E, 256), 1)
     ok_plain = bool(np.array_equal(out.view, exp))
     out.view[:] = -1
-    run("event_pipeline_4_blobs", lambda: g.compute(cr, 2, "mandelbrot", npx // E, 256, 0, True, ck.PIPELINE_EVENT, 4), 2)
+    run("event_pipeline_4_blobs", lambda: g.compute(cr, 2, MK, npx // E, 256, 0, True, ck.PIPELINE_EVENT, 4), 2)
     ok_pipe = bool(np.array_equal(out.view, exp))
     del res["event_pipeline_4_blobs"]["us_per_call_device_span"], res["event_pipeline_4_blobs"]["us_host_overhead_per_call"]  # host clock there
     rw = ["", ""]
-    run("resident_kernel_only", lambda: g.compute(cr, 3, "mandelbrot", npx // E, 256, 0, False, True, 4, readWritesReady=rw,
+    run("resident_kernel_only", lambda: g.compute(cr, 3, MK, npx // E, 256, 0, False, True, 4, readWritesReady=rw,
                                                   elementsPerItemReady=[1, E]), 3)
     k = res["resident_kernel_only"]["us_per_call_device_span"] * 1e-6
     peak = 2.0 * 128 * sms * pk["sm_max_mhz"] * 1e6 / 1e12
@@ -774,7 +775,7 @@ def run_ours(args):
     shares, imbalance = [], []
 
     def step_resident():
-        assert g.compute(cr, CID_RES, "mandelbrot", items, 256, 0, False, True, 4, readWritesReady=rw_res, elementsPerItemReady=[1, E]) == 0
+        assert g.compute(cr, CID_RES, MK, items, 256, 0, False, True, 4, readWritesReady=rw_res, elementsPerItemReady=[1, E]) == 0
         t_local = cr.benchmarks(CID_RES)
         return t_local
 
@@ -824,7 +825,7 @@ def run_ours(args):
     def step_e2e():
         barrier()
         t0 = time.perf_counter()
-        assert g.compute(cr, CID_E2E, "mandelbrot", items, 256, 0, True, args.e2e_mode == "event", args.e2e_blobs) == 0
+        assert g.compute(cr, CID_E2E, MK, items, 256, 0, True, args.e2e_mode == "event", args.e2e_blobs) == 0
         dt = allmax(time.perf_counter() - t0)
         tt = cr_times(cr, CID_E2E, cr.benchmarks(CID_E2E), spmd_mode,
                       allgather=(lambda v: gather(dist, torch, torch_dev, v, world)) if spmd_mode else None)
@@ -867,7 +868,7 @@ def run_ours(args):
             "traffic": ncu_traffic("mandelbrot") if n_gpus == 1 else None,
             "traffic_note": "DRAM read+write bytes of one launch (ncu --set full, profiles/r1_ncu_summary.json); the algorithmic "
                             "output is 4 B x 2^28 pixels = 1.074e9 B",
-            "kernel": "mandelbrot", "per_gpu": True,
+            "kernel": MK, "per_gpu": True,
             "algorithmic": f"8 FLOP x {int(total_iters)} executed iterations (sum of the output counts, bit-exact with the oracle)",
             "peak_source": f"2 x 128 lanes x {sms} SMs x {pk['sm_max_mhz']:.0f} MHz ({pk['source']}); no tensor cores on this path",
             "frac_at_observed_clock": (ach / (2.0 * 128 * sms * clk["sm_mhz"] * 1e6 / 1e12)) if clk.get("sm_mhz") else None}
@@ -928,7 +929,7 @@ def run_ours(args):
             "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
             "dtype": "f32", "data": "synthetic",
             "config": {"workload": f"mandelbrot {W}x{H} maxIter {MAX_ITER} view [-2,1]x[-1.5,1.5] (BASELINE configs[2]), "
-                                   f"{E} pixels per work-item, local 256, via ClNumberCruncher.compute",
+                                   f"kernel {MK}, {E} pixel(s) per work-item, local 256, via ClNumberCruncher.compute",
                        "parallelism": ("spmd one process per GPU" if spmd_mode else "one process") + f" x{n_gpus}",
                        "l2": "output 1 GiB per step >> 126 MB L2, no reuse between steps",
                        "balancer": args.balancer, "balancer_settle_steps": settle, "host_memory_policy_rank0": numa},
@@ -1001,12 +1002,16 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--balancer", default="profile", choices=["profile", "adaptive", "reference"])
+    ap.add_argument("--mandel-kernel", default="mandelbrot1", choices=["mandelbrot1", "mandelbrot"],
+                    help="mandelbrot1: one pixel per work-item (round 2); mandelbrot: four pixels of a row per work-item (round 1)")
     ap.add_argument("--no-all", dest="all", action="store_false", help="skip the SAXPY and n-body workloads")
     ap.add_argument("--e2e-blobs", type=int, default=16, help="pipeline blobs of the end-to-end leg (multiple of 4)")
     ap.add_argument("--e2e-mode", default="event", choices=["event", "driver"], help="pipelining mode of the end-to-end leg")
     ap.add_argument("--only", default=None, choices=["nbody", "saxpy", "pipeline", "hostlink", "c1", "image"],
                     help="profiling aid: run just this secondary workload on one GPU and print its numbers")
     args = ap.parse_args()
+    global E, MK
+    MK, E = args.mandel_kernel, (4 if args.mandel_kernel == "mandelbrot" else 1)
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
     # stdout carries exactly ONE JSON line: libraries that print banners there (NCCL's version line) go to stderr
     global _REAL_STDOUT

@@ -113,7 +113,14 @@ __kernel void mandelbrot(const float* __restrict__ view, int* __restrict__ out)
     *reinterpret_cast<int4*>(out + p0) = make_int4(r[0], r[1], r[2], r[3]);
 }
 
-// 1 pixel per work-item variant (numberOfElementsPerWorkItem = 1), for callers that want the plain mapping
+// One pixel per work-item (numberOfElementsPerWorkItem = 1): the form the benchmark uses from round 2 on.
+// A work-item of `mandelbrot` runs its four pixels one after the other, so a work-group inside the set lasts 4 x maxIter
+// iterations (0.5 ms at 4096); when a launch runs out of work-groups every SM idles until its slowest one ends — 2 % of a
+// 24 ms launch, but 7 % of the 3.3 ms share one of eight GPUs gets — and a warp covers 128 pixels of one row, the longest
+// cut through the set's boundary (29.9 of 32 lanes active per instruction).  Here the serial length of a work-group is
+// maxIter iterations and a warp covers 32 pixels.  Measured on B200, 16384^2 x 4096 (profiles/r2_mandelbrot_kernels_1gpu.md):
+// mandelbrot 24.05 ms (82.9 % of the FP32 peak), this kernel 23.02 ms (86.7 %); a variant that also gave every warp an
+// 8 x 4 pixel footprint inside 32 x 8 tiles was slower (23.61 ms) and was dropped.
 __kernel void mandelbrot1(const float* __restrict__ view, int* __restrict__ out)
 {
     const float x0 = __ldg(view + 0), y0 = __ldg(view + 1), dx = __ldg(view + 2), dy = __ldg(view + 3);

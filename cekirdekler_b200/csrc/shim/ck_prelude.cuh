@@ -212,4 +212,47 @@ __device__ __forceinline__ float degrees(float r) { return r * 57.29577951308232
 __device__ __forceinline__ float radians(float d) { return d * 0.017453292519943295f; }
 template <typename T> __device__ __forceinline__ T select(T a, T b, int c) { return c ? b : a; }
 
+// ---- component selections beyond .x .y .z .w (OpenCL C 6.1.7) ----
+// The host side rewrites `e.xy`, `e.zw`, `e.lo`, `e.hi`, `e.xyz` into ck_xy(e) ... (and `.s0`..`.s3` into `.x`..`.w`).  On an
+// lvalue the result is a pair/triple of references that converts to the narrower vector and can be assigned one; on an
+// rvalue it is the narrower vector itself.  A struct of the user's own that has a member called lo, hi, xy ... keeps it.
+template <class V2, class S> struct ck_sel2 {
+    S& a; S& b;
+    __device__ __forceinline__ operator V2() const { V2 r; r.x = a; r.y = b; return r; }
+    __device__ __forceinline__ ck_sel2& operator=(const V2& v) { a = v.x; b = v.y; return *this; }
+    __device__ __forceinline__ ck_sel2& operator=(const ck_sel2& o) { const S t0 = o.a, t1 = o.b; a = t0; b = t1; return *this; }
+};
+template <class V3, class S> struct ck_sel3 {
+    S& a; S& b; S& c;
+    __device__ __forceinline__ operator V3() const { V3 r; r.x = a; r.y = b; r.z = c; return r; }
+    __device__ __forceinline__ ck_sel3& operator=(const V3& v) { a = v.x; b = v.y; c = v.z; return *this; }
+};
+#define CK_SWIZZLES(B)                                                                                                        \
+    __device__ __forceinline__ ck_sel2<B##2, B> ck_xy(B##4& v) { return {v.x, v.y}; }                                         \
+    __device__ __forceinline__ ck_sel2<B##2, B> ck_zw(B##4& v) { return {v.z, v.w}; }                                         \
+    __device__ __forceinline__ ck_sel2<B##2, B> ck_lo(B##4& v) { return {v.x, v.y}; }                                         \
+    __device__ __forceinline__ ck_sel2<B##2, B> ck_hi(B##4& v) { return {v.z, v.w}; }                                         \
+    __device__ __forceinline__ ck_sel3<B##3, B> ck_xyz(B##4& v) { return {v.x, v.y, v.z}; }                                   \
+    __device__ __forceinline__ ck_sel2<B##2, B> ck_xy(B##3& v) { return {v.x, v.y}; }                                         \
+    __device__ __forceinline__ B##2 ck_xy(const B##4& v) { return make_##B##2(v.x, v.y); }                                    \
+    __device__ __forceinline__ B##2 ck_zw(const B##4& v) { return make_##B##2(v.z, v.w); }                                    \
+    __device__ __forceinline__ B##2 ck_lo(const B##4& v) { return make_##B##2(v.x, v.y); }                                    \
+    __device__ __forceinline__ B##2 ck_hi(const B##4& v) { return make_##B##2(v.z, v.w); }                                    \
+    __device__ __forceinline__ B##3 ck_xyz(const B##4& v) { return make_##B##3(v.x, v.y, v.z); }                              \
+    __device__ __forceinline__ B##2 ck_xy(const B##3& v) { return make_##B##2(v.x, v.y); }                                    \
+    __device__ __forceinline__ B& ck_lo(B##2& v) { return v.x; }                                                              \
+    __device__ __forceinline__ B& ck_hi(B##2& v) { return v.y; }                                                              \
+    __device__ __forceinline__ B ck_lo(const B##2& v) { return v.x; }                                                         \
+    __device__ __forceinline__ B ck_hi(const B##2& v) { return v.y; }
+CK_SWIZZLES(float)
+CK_SWIZZLES(double)
+CK_SWIZZLES(int)
+CK_SWIZZLES(uint)
+// fall-backs: user structs with members of these names
+template <class T> __device__ __forceinline__ auto ck_xy(T&& v) -> decltype((v.xy)) { return v.xy; }
+template <class T> __device__ __forceinline__ auto ck_zw(T&& v) -> decltype((v.zw)) { return v.zw; }
+template <class T> __device__ __forceinline__ auto ck_lo(T&& v) -> decltype((v.lo)) { return v.lo; }
+template <class T> __device__ __forceinline__ auto ck_hi(T&& v) -> decltype((v.hi)) { return v.hi; }
+template <class T> __device__ __forceinline__ auto ck_xyz(T&& v) -> decltype((v.xyz)) { return v.xyz; }
+
 #endif  // CK_PRELUDE_CUH

@@ -92,6 +92,58 @@ std::string rewrite_kernels(const std::string& src, std::vector<std::pair<std::s
                 continue;
             }
         }
+        // OpenCL C component selections CUDA's vector structs lack: `.s0`..`.s3` become `.x`..`.w`; `.xy .zw .lo .hi .xyz` wrap
+        // the postfix expression they follow into ck_xy(...) etc., which the prelude defines for the float/int/uint vectors
+        // (readable and assignable) and, as a fall-back, for any struct that has a member of that name.
+        bool after_operand = src[i] == '.' && i > 0 && i + 2 < n && (ident_char(src[i - 1]) || src[i - 1] == ')' || src[i - 1] == ']');
+        if (after_operand && ident_char(src[i - 1])) {   // `1.5f`, `2.` are numbers, not operands
+            size_t k = i;
+            while (k > 0 && ident_char(src[k - 1])) k--;
+            if (std::isdigit((unsigned char)src[k])) after_operand = false;
+        }
+        if (after_operand) {
+            size_t e = i + 1;
+            while (e < n && ident_char(src[e])) e++;
+            const std::string word = src.substr(i + 1, e - i - 1);
+            if (word.size() == 2 && word[0] == 's' && word[1] >= '0' && word[1] <= '3') {
+                out.push_back('.');
+                out.push_back("xyzw"[word[1] - '0']);
+                i = e;
+                continue;
+            }
+            if (word == "xy" || word == "zw" || word == "lo" || word == "hi" || word == "xyz") {
+                // walk back over the postfix expression already copied to `out`: names, a.b, a->b, f(...), a[...]
+                size_t j = out.size();
+                for (;;) {
+                    if (j > 0 && (out[j - 1] == ')' || out[j - 1] == ']')) {
+                        const char close = out[j - 1], open = close == ')' ? '(' : '[';
+                        int depth = 0;
+                        size_t k = j;
+                        while (k > 0) {
+                            k--;
+                            if (out[k] == close) depth++;
+                            else if (out[k] == open && --depth == 0) break;
+                        }
+                        if (depth != 0) break;
+                        j = k;
+                        continue;
+                    }
+                    size_t k = j;
+                    while (k > 0 && ident_char(out[k - 1])) k--;
+                    if (k == j) break;
+                    j = k;
+                    if (j > 0 && out[j - 1] == '.') { j--; continue; }
+                    if (j > 1 && out[j - 1] == '>' && out[j - 2] == '-') { j -= 2; continue; }
+                    break;
+                }
+                if (j < out.size()) {
+                    out.insert(j, "ck_" + word + "(");
+                    out.push_back(')');
+                    i = e;
+                    continue;
+                }
+            }
+        }
         // candidate token start?
         bool at_token_start = (i == 0) || !ident_char(src[i - 1]);
         size_t tok = 0;
@@ -210,6 +262,20 @@ std::shared_ptr<Cubin> compile_source(const std::string& user_src, int cc_major,
         if (it != g_cache.end()) return it->second;
     }
     auto cb = std::make_shared<Cubin>();
+    // OpenCL 2.0 device-side enqueue (the reference looks for this very token to make a default device queue,
+    // ClNumberCruncher.cs:203-205, Worker.cs:224-227) has no translation here: CUDA's counterpart is dynamic parallelism
+    // (`child<<<grid, block>>>(...)` inside a kernel), which needs relocatable device code linked against cudadevrt, and the
+    // blocks/ndrange_t argument forms do not map onto it textually.  Say so instead of failing on an undefined identifier.
+    {
+        const size_t at = user_src.find("enqueue_kernel");
+        if (at != std::string::npos && (at == 0 || !ident_char(user_src[at - 1])) && user_src.find('(', at) != std::string::npos) {
+            cb->err = 2000;
+            cb->log = "Kernel source uses enqueue_kernel(...): OpenCL 2.0 device-side enqueue is not supported by libKutuphaneCL.so on CUDA.\n"
+                      "Launch the child work from the host as a second kernel name of the same compute() call (\"parent child\"), "
+                      "or restructure the parent to loop over the child's range.";
+            return cb;
+        }
+    }
     std::string body = rewrite_kernels(user_src, &cb->kernels);
     std::string full = std::string(kPrelude) + "\n#line 1 \"user_kernels.cu\"\n" + body;
 

@@ -111,6 +111,37 @@ def test_mandelbrot_multi_gpu_balanced_and_pipelined(gpus):
         assert np.array_equal(got, exp)
 
 
+@pytest.mark.parametrize("W,H", [(1024, 1024), (256, 64), (512, 23), (96, 96), (2048, 2048)])
+def test_mandelbrot_one_pixel_kernel_bit_exact(gpus, W, H):
+    """mandelbrot1 (the benchmark's kernel): same counts as the oracle on one device and on all, plain and pipelined."""
+    it = 300
+    exp = po.mandelbrot(po.mandelbrot_view(W, H, it), W * H)
+    for devs in (gpu0(), all_gpus()):
+        got, cr = run_mandelbrot(devs, W, H, it, "mandelbrot1", calls=3)
+        assert np.array_equal(got, exp)
+        if W * H >= 256 * 8 * len(cr.globalRanges(1)):
+            for ptype in (True, False):
+                got, _ = run_mandelbrot(devs, W, H, it, "mandelbrot1", calls=2, pipeline=True, pipeline_type=ptype, blobs=4)
+                assert np.array_equal(got, exp)
+
+
+def test_mandelbrot_with_a_range_offset(gpus):
+    """A compute() that starts in the middle of the image (global offset) and covers a ragged number of rows."""
+    W, H, it = 512, 64, 200
+    v = po.mandelbrot_view(W, H, it)
+    exp = po.mandelbrot(v, W * H)
+    cr = ck.ClNumberCruncher(gpu0(), kernels.source("mandelbrot"))
+    view, out = ck.ClArray(8, np.float32), ck.ClArray(W * H, np.int32)
+    view.view[:] = v
+    view.readOnly = True
+    out.writeOnly = True
+    out.view[:] = -1
+    first, count = 3 * W + 256, 41 * W + 256
+    assert view.nextParam(out).compute(cr, 1, "mandelbrot1", count, 256, first) == 0
+    assert np.array_equal(out.view[first:first + count], exp[first:first + count])
+    assert (out.view[:first] == -1).all() and (out.view[first + count:] == -1).all()
+
+
 # ------------------------------------------------------------------ vector-add / SAXPY (K2, K3)
 def test_reference_vector_add_test(gpus):
     """Tester.stream_C_equals_A_plus_B_1M_elements (Tester.cs:7806-7843): API style 2 flag strings, driver pipeline with

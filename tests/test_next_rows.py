@@ -105,3 +105,57 @@ def test_compute_follows_an_array_that_was_resized_or_switched(gpus):
     b.view[:] = 0
     assert a.nextParam(b).compute(cr, 1, "test", 2 * n, 256) == 0
     assert np.array_equal(b.view, a.view)
+
+
+def test_component_selections_compute_what_opencl_says(gpus):
+    """§8(f) row 1: `.xy .zw .lo .hi .xyz .s0-.s3` as values and as assignment targets."""
+    src = """
+    __kernel void swz(__global float4* v, __global float2* o, __global float* s)
+    {
+        int i = get_global_id(0);
+        float4 a = v[i];
+        float2 p = a.xy + a.zw;
+        float2 q = v[i].lo * 2.0f - (a * 2.0f).hi;
+        a.zw = p;
+        a.lo = (float2)(a.s3, a.s0);
+        float3 t = a.xyz;
+        o[i] = p + q + (float2)(t.x, t.z);
+        s[i] = a.s0 + a.s1 + a.s2 + a.s3 + p.lo + q.hi;
+        v[i] = a;
+    }"""
+    n = 1 << 12
+    cr = ck.ClNumberCruncher(ck.ClPlatforms.all().gpus(), src)
+    assert cr.errorCode() == 0, cr.errorMessage()
+    v, o, s = ck.ClArray(4 * n, np.float32), ck.ClArray(2 * n, np.float32), ck.ClArray(n, np.float32)
+    v0 = (np.arange(4 * n, dtype=np.float32) % 13).reshape(n, 4)
+    v.view[:] = v0.reshape(-1)
+    v.numberOfElementsPerWorkItem, o.numberOfElementsPerWorkItem = 4, 2
+    v.partialRead, v.read = True, False
+    o.writeOnly, s.writeOnly = True, True
+    assert v.nextParam(o, s).compute(cr, 1, "swz", n, 256) == 0
+    x, y, z, w = v0[:, 0], v0[:, 1], v0[:, 2], v0[:, 3]
+    p = np.stack([x + z, y + w], 1)
+    q = np.stack([2 * x - 2 * z, 2 * y - 2 * w], 1)
+    a = np.stack([p[:, 1], x, p[:, 0], p[:, 1]], 1)            # zw = p, then lo = (s3, s0) = (p.y, x)
+    assert np.array_equal(v.view.reshape(n, 4), a)
+    assert np.array_equal(o.view.reshape(n, 2), p + q + np.stack([a[:, 0], a[:, 2]], 1))
+    assert np.array_equal(s.view, a.sum(1) + p[:, 0] + q[:, 1])
+
+
+def test_readme_hello_world_prints_from_every_work_item(gpus, capfd):
+    """The README's first example (/root/reference/README.md:52-59): 1000 work-items in groups of 100, shared by all GPUs,
+    each printing "hello world" through the device's printf."""
+    src = """
+                    __kernel void hello(__global char * arr)
+                    {
+                        printf("hello world");
+                    }
+                """
+    cr = ck.ClNumberCruncher(ck.ClPlatforms.all().gpus(), src)
+    assert cr.errorCode() == 0, cr.errorMessage()
+    array = ck.ClArray(1000, np.uint8)
+    assert array.compute(cr, 1, "hello", 1000, 100) == 0
+    cr.sync()
+    cr.dispose()                         # the device's printf buffer is flushed at synchronisation points
+    out = capfd.readouterr().out
+    assert out.count("hello world") == 1000

@@ -109,3 +109,42 @@ def test_opencl_c_idioms_compile_through_the_prelude():
 def test_build_errors_are_reported_not_thrown():
     rc, log, nbytes = compile_check("__kernel void broken(__global float* a) { a[0] = undefined_symbol; }")
     assert rc != 0 and "undefined_symbol" in log and nbytes == 0
+
+
+def test_component_selections_and_the_readme_sample_compile():
+    """`.xy .zw .lo .hi .xyz .s0-.s3` on values and as assignment targets (OpenCL C 6.1.7), a user struct that has a member
+    called `lo` of its own, and the README's first example (/root/reference/README.md:52-59)."""
+    src = """
+    struct Range { float lo; float hi; };
+    __kernel void swz(__global float4* v, __global float2* o, __global float* s)
+    {
+        int i = get_global_id(0);
+        float4 a = v[i];
+        float2 p = a.xy + a.zw;
+        float2 q = v[i].lo * 2.0f - (a * 2.0f).hi;
+        a.zw = p;
+        a.lo = (float2)(a.s3, a.s0);
+        float3 t = a.xyz;
+        struct Range r; r.lo = t.x; r.hi = t.y + 1.5f;
+        o[i] = p + q + (float2)(r.lo, r.hi);
+        s[i] = a.s0 + a.s1 + a.s2 + a.s3 + p.lo + q.hi + 1.5f;
+        v[i] = a;
+    }
+    __kernel void hello(__global char * arr)
+    {
+        printf("hello world");
+    }"""
+    rc, log, _ = compile_check(src)
+    assert rc == 0, log
+
+
+def test_device_side_enqueue_is_refused_with_a_clear_message():
+    src = """
+    __kernel void child(__global int* a) { a[get_global_id(0)] = 1; }
+    __kernel void parent(__global int* a)
+    {
+        enqueue_kernel(get_default_queue(), CLK_ENQUEUE_FLAGS_NO_WAIT, ndrange_1D(64), ^{ child(a); });
+    }"""
+    rc, log, nbytes = compile_check(src)
+    assert rc != 0 and nbytes == 0
+    assert "enqueue_kernel" in log and "not supported" in log
