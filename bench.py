@@ -568,7 +568,10 @@ def bench_nbody(ck, kernels, po, devs, pk, sms, steps, warmup, spmd_attach=None,
                 defer_finish=False):
     """C4: all-pairs n-body, 128 Ki bodies float4; pos is a whole-array read, vel/posOut are sliced."""
     n = 131072
-    cr = ck.ClNumberCruncher(devs, kernels.source("nbody"))
+    nb_src = kernels.source("nbody")
+    if os.environ.get("CK_NBW_TPW"):        # experiment hook: j tiles per warp and unit (profiles/r2_nbody_unit_size.md)
+        nb_src = f"// ck-nvrtc: -DNBW_TILES_PER_WARP={int(os.environ['CK_NBW_TPW'])}\n" + nb_src
+    cr = ck.ClNumberCruncher(devs, nb_src)
     assert cr.errorCode() == 0, cr.errorMessage()
     cr.balancerMode = 2
     if spmd_attach:
@@ -865,8 +868,8 @@ def run_ours(args):
     ach = flops / n_gpus / kernel_s / 1e12     # per-GPU rate (each GPU runs its share concurrently)
     clk = clocks.summary()
     roof = {"bound": "fp32", "achieved": ach, "peak": peak_tf, "unit": "TFLOP/s", "frac": ach / peak_tf,
-            "traffic": ncu_traffic("mandelbrot") if n_gpus == 1 else None,
-            "traffic_note": "DRAM read+write bytes of one launch (ncu --set full, profiles/r1_ncu_summary.json); the algorithmic "
+            "traffic": (ncu_traffic("mandelbrot1", "r2_ncu_summary.json") if MK == "mandelbrot1" else ncu_traffic("mandelbrot")) if n_gpus == 1 else None,
+            "traffic_note": "DRAM read+write bytes of one launch (ncu --set full, profiles/r2_ncu_summary.json / r1_ncu_summary.json); the algorithmic "
                             "output is 4 B x 2^28 pixels = 1.074e9 B",
             "kernel": MK, "per_gpu": True,
             "algorithmic": f"8 FLOP x {int(total_iters)} executed iterations (sum of the output counts, bit-exact with the oracle)",

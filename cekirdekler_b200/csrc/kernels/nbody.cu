@@ -334,7 +334,9 @@ __kernel void nBody3Dq(const float4* __restrict__ pos, float4* __restrict__ vel,
 #define NBW_GROUP 128            // bodies per unit: 32 lanes x NB_B
 #define NBW_MAXW 8               // warps per work-group at most
 #define NBW_HDR 4                // ints before the per-group counters
+#ifndef NBW_TILES_PER_WARP
 #define NBW_TILES_PER_WARP 2     // j tiles a warp sweeps per unit
+#endif
 
 // The step itself, shared by nBody3Dw and nBody3Dwp (below).  With NBW_PEERS the integrating work-group also stores each
 // new position into the posOut buffers of the other devices (peers[0] = count, peers[1..] = device pointers, NVLink peer

@@ -1,7 +1,10 @@
 #!/usr/bin/env python
-"""Condense `ncu -i X.ncu-rep --page raw --csv` pages (one launch each) into profiles/r1_ncu_summary.json.
+"""Condense `ncu -i X.ncu-rep --page raw --csv` pages into profiles/r1_ncu_summary.json (or `--out NAME.json`).
 
     python profiles/make_summary.py mandelbrot=profiles/r1_ncu_mandelbrot_full_raw.csv saxpy=... nbody=...
+    python profiles/make_summary.py --out r2_ncu_summary.json blurStrips=profiles/r2_ncu_image_raw.csv@blurStrips ...
+
+`name=path@text` keeps only the launches whose kernel name contains `text` (a report with several kernels).
 
 bench.py reads `traffic_B` (dram__bytes_read.sum + dram__bytes_write.sum of ONE launch) from the summary for
 `roofline.traffic`; the other fields are the ones DESIGN.md quotes."""
@@ -13,9 +16,12 @@ from pathlib import Path
 UNIT = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9, "ns": 1e-9, "us": 1e-6, "ms": 1e-3, "s": 1.0, "second": 1.0}
 
 
-def summarize(path):
+def summarize(path, only=None):
     rows = list(csv.reader(open(path)))
     hdr, units = rows[0], rows[1]
+    if only:
+        kcol = hdr.index("Kernel Name")
+        rows = rows[:2] + [r for r in rows[2:] if only in r[kcol]]
     # several launches in one report: keep the longest (the resident, whole-range launch)
     tcol = hdr.index("gpu__time_duration.sum")
     row = max(rows[2:], key=lambda r: float(r[tcol].replace(",", "")) * UNIT.get(units[tcol], 1.0))
@@ -46,11 +52,16 @@ def summarize(path):
 
 
 if __name__ == "__main__":
-    out_path = Path(__file__).resolve().parent / "r1_ncu_summary.json"
+    argv = sys.argv[1:]
+    out_name = "r1_ncu_summary.json"
+    if argv and argv[0] == "--out":
+        out_name, argv = argv[1], argv[2:]
+    out_path = Path(__file__).resolve().parent / out_name
     out = json.loads(out_path.read_text()) if out_path.exists() else {}
-    for arg in sys.argv[1:]:
+    for arg in argv:
         name, path = arg.split("=", 1)
-        out[name] = summarize(path)
+        path, _, only = path.partition("@")
+        out[name] = summarize(path, only or None)
         out[name]["source"] = str(Path(path).name)
     out_path.write_text(json.dumps(out, indent=1) + "\n")
     print(json.dumps(out, indent=1))

@@ -83,6 +83,33 @@ def test_devices_sorted_by_nbody_micro_benchmark(gpus):
     devs = ck.ClPlatforms.all().gpus()
     ranked = devs.devicesWithHighestDirectNbodyPerformance(4096)
     assert sorted(ranked.ordinals) == sorted(devs.ordinals)
+    if gpus < 2:
+        return
+    # the order must follow the measurement: keep device 0 busy with someone else's kernels while the ranking runs,
+    # and it has to come out last
+    import threading
+
+    load = ck.ClNumberCruncher(devs[0], """
+        __kernel void burn(__global float* a) { int i = get_global_id(0); float v = a[i];
+            for (int k = 0; k < 40000; k++) v = v * 1.0000001f + 1e-7f; a[i] = v; }""")
+    assert load.errorCode() == 0, load.errorMessage()
+    a = ck.ClArray(1 << 20, np.float32)
+    a.read, a.write = False, False
+    stop = threading.Event()
+
+    def burn():
+        while not stop.is_set():
+            a.compute(load, 1, "burn", 1 << 20, 256)
+
+    th = threading.Thread(target=burn)
+    th.start()
+    try:
+        ranked = devs.devicesWithHighestDirectNbodyPerformance(16384)
+    finally:
+        stop.set()
+        th.join()
+    assert ranked.ordinals[-1] == devs.ordinals[0], ranked.ordinals
+    load.dispose()
 
 
 def test_compute_follows_an_array_that_was_resized_or_switched(gpus):
