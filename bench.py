@@ -755,6 +755,8 @@ def run_ours(args):
     cr = ck.ClNumberCruncher(devs, kernels.source("mandelbrot"))
     assert cr.errorCode() == 0, cr.errorMessage()
     cr.balancerMode = {"reference": 0, "adaptive": 1, "profile": 2}[args.balancer]
+    if args.no_smooth:
+        cr.smoothLoadBalancer = False            # ClNumberCruncher.smoothLoadBalancer (ClNumberCruncher.cs:151-159)
     if spmd_mode:
         spmd.attach(cr, rank, world, torch_dev)
     npix = W * H
@@ -791,7 +793,7 @@ def run_ours(args):
     # The throughput figure is the steady state, so extra UNTIMED calls run until the split has settled (max/mean device
     # time <= 1.03 twice in a row, at most 16 calls); their number is disclosed in config.balancer_settle_steps.
     settle = 0
-    while n_gpus > 1 and settle < 16 and not (len(imbalance) >= 2 and max(imbalance[-2:]) <= 1.03):
+    while n_gpus > 1 and settle < args.max_settle and not (len(imbalance) >= 2 and max(imbalance[-2:]) <= 1.03):
         t = step_resident()
         tt = cr_times(cr, CID_RES, t, spmd_mode, allgather=(lambda v: gather(dist, torch, torch_dev, v, world)) if spmd_mode else None)
         shares.append(cr.globalRanges(CID_RES))
@@ -837,7 +839,7 @@ def run_ours(args):
 
     for _ in range(args.warmup):
         step_e2e()
-    while n_gpus > 1 and e2e_settle < 16 and not (len(e2e_imb) >= 2 and max(e2e_imb[-2:]) <= 1.03):
+    while n_gpus > 1 and e2e_settle < args.max_settle and not (len(e2e_imb) >= 2 and max(e2e_imb[-2:]) <= 1.03):
         step_e2e()
         e2e_settle += 1
     for _ in range(args.steps):
@@ -935,7 +937,7 @@ def run_ours(args):
                                    f"kernel {MK}, {E} pixel(s) per work-item, local 256, via ClNumberCruncher.compute",
                        "parallelism": ("spmd one process per GPU" if spmd_mode else "one process") + f" x{n_gpus}",
                        "l2": "output 1 GiB per step >> 126 MB L2, no reuse between steps",
-                       "balancer": args.balancer, "balancer_settle_steps": settle, "host_memory_policy_rank0": numa},
+                       "balancer": args.balancer, "smooth_load_balancer": not args.no_smooth, "balancer_settle_steps": settle, "host_memory_policy_rank0": numa},
             "wall_ms_per_step": wall / args.steps * 1e3,
             "clocks": clk,
             "e2e": {"value": e2e_value, "unit": UNIT, "ms_per_step": e2e_ms, "h2d_bytes_per_step": 32 * n_gpus,
@@ -1007,6 +1009,8 @@ def main():
     ap.add_argument("--balancer", default="profile", choices=["profile", "adaptive", "reference"])
     ap.add_argument("--mandel-kernel", default="mandelbrot1", choices=["mandelbrot1", "mandelbrot"],
                     help="mandelbrot1: one pixel per work-item (round 2); mandelbrot: four pixels of a row per work-item (round 1)")
+    ap.add_argument("--no-smooth", action="store_true", help="smoothLoadBalancer = false (the reference's default is true)")
+    ap.add_argument("--max-settle", type=int, default=16, help="untimed balancer calls allowed before the timed steps (0: time from the start)")
     ap.add_argument("--no-all", dest="all", action="store_false", help="skip the SAXPY and n-body workloads")
     ap.add_argument("--e2e-blobs", type=int, default=16, help="pipeline blobs of the end-to-end leg (multiple of 4)")
     ap.add_argument("--e2e-mode", default="event", choices=["event", "driver"], help="pipelining mode of the end-to-end leg")
