@@ -403,13 +403,19 @@ class ClParameterGroup:
                 localRange: int = 256, ofsetGlobalRange: int = 0, pipeline: bool = False, pipelineType: bool = PIPELINE_EVENT,
                 pipelineBlobs: int = 4, readWritesReady=None, elementsPerItemReady=None) -> int:
         n = len(self._arrays)
-        arrs = (C.c_void_p * n)(*[a._handle for a in self._arrays])
-        flags = list(readWritesReady) if readWritesReady is not None else self._flags
-        elems = list(elementsPerItemReady) if elementsPerItemReady is not None else self._elems
-        rw = (C.c_char_p * n)(*[f.encode() for f in flags])
-        ep = (C.c_int32 * n)(*elems)
-        return host().ckh_compute(cruncher._handle, arrs, n, computeId, kernelNamesString.encode(), globalRange, localRange,
-                                  ofsetGlobalRange, int(pipeline), int(pipelineType), pipelineBlobs, rw, ep)
+        flags = readWritesReady if readWritesReady is not None else self._flags
+        elems = elementsPerItemReady if elementsPerItemReady is not None else self._elems
+        # the marshalled argument block is kept between calls: a ~50 us kernel is called thousands of times with the same
+        # arrays and flags (SURVEY.md §7 hard part 6), and building four ctypes arrays costs several microseconds
+        key = (tuple(flags), tuple(elems), kernelNamesString)
+        handles = [a._handle for a in self._arrays]
+        m = getattr(self, "_marshalled", None)
+        if m is None or m[0] != key or m[1] != handles:
+            m = (key, handles, (C.c_void_p * n)(*handles), (C.c_char_p * n)(*[f.encode() for f in flags]), (C.c_int32 * n)(*elems),
+                 kernelNamesString.encode())
+            self._marshalled = m
+        return host().ckh_compute(cruncher._handle, m[2], n, computeId, m[5], globalRange, localRange,
+                                  ofsetGlobalRange, int(pipeline), int(pipelineType), pipelineBlobs, m[3], m[4])
 
 
 # ----------------------------------------------------------------------------- cruncher
