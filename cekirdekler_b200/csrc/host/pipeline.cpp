@@ -74,6 +74,9 @@ void ClPipelineStage::appendToStage(ClPipelineStage* stage) {
 }
 
 ClPipelineStage::~ClPipelineStage() {
+    for (int b = 0; b < 2; b++)
+        for (ck_handle e : {compDone_[b], inDone_[b], outDone_[b]})
+            if (e) deleteEvent(e);
     if (forwardQueue_) {
         finish(forwardQueue_);
         deleteCommandQueue(forwardQueue_);
@@ -94,6 +97,15 @@ ClPipeline* ClPipelineStage::makePipeline(Forwarding mode) {
     }
     p->mode_ = mode;
     for (auto* s : p->stages_) s->init(mode);
+    const char* env = getenv("CK_PIPELINE_CHAINED");
+    p->chained_ = mode == Forwarding::PeerToPeer && !(env && env[0] == '0');
+    if (p->chained_)
+        for (auto* s : p->stages_)
+            for (int b = 0; b < 2; b++) {
+                if (!s->compDone_[b]) s->compDone_[b] = createEvent();
+                if (!s->inDone_[b]) s->inDone_[b] = createEvent();
+                if (!s->outDone_[b]) s->outDone_[b] = createEvent();
+            }
     return p;
 }
 
@@ -208,6 +220,7 @@ bool ClPipeline::pushData(const std::vector<void*>& data, const std::vector<void
         return false;
     }
     const bool hasData = !data.empty(), hasPop = !popResultsHere.empty();
+    if (chained_) return pushChained(data, popResultsHere);
 
     // 1) every stage computes on its `buf`s — enqueued without host synchronisation, so all devices run concurrently
     for (auto* s : stages_) {
@@ -270,12 +283,96 @@ bool ClPipeline::pushData(const std::vector<void*>& data, const std::vector<void
             for (auto& b : stages_[i]->outputs_) b->switchBuffers();
     }
 
+    return finishPush(hasData, hasPop);
+}
+
+bool ClPipeline::finishPush(bool hasData, bool hasPop) {
+    const int S = (int)stages_.size();
     counter++;
     if ((counter > (S * 2 - 2)) && !hasData && !hasPop) return true;
     if ((counter > (S * 2 - 1)) && hasData && !hasPop) return true;
     if ((counter > (S * 2 - 1)) && !hasData && hasPop) return true;
     if ((counter > (S * 2)) && hasData && hasPop) return true;
     return false;
+}
+
+ClPipeline::~ClPipeline() {
+    if (!chained_) return;
+    for (auto* s : stages_) {          // nothing of this pipeline is left in flight when its stages are reused or destroyed
+        if (s->cruncher_) s->cruncher_->setEnqueueMode(false);
+        if (s->forwardQueue_) finish(s->forwardQueue_);
+    }
+}
+
+// Peer-to-peer forwarding without a host join per push.  What a push touches (ClPipeline.cs:49-125): stage k's kernels read
+// its input `buf`s and write its output `buf`s; the hand-off k -> k+1 copies k's output DUPLICATES (= the `buf`s of the push
+// before, the pointers are swapped at the end of every push) into k+1's input duplicates (= its `buf`s of the next push).
+// So nothing inside one push depends on anything else in it, and push p depends on push p-1 only through
+//     kernels(k, p)      after  hand-off into k (p-1)  [its input]   and  hand-off out of k (p-1)  [still reading the buffer it overwrites]
+//     hand-off(k->k+1, p) after  kernels(k, p-1)       [its source]   and  kernels(k+1, p-1)        [still reading the buffer it overwrites]
+// (upload into stage 0 and download from the last stage count as hand-offs).  These are event waits on the devices; the
+// host waits only for what it must see itself — the upload of `data` (the caller may reuse those arrays on return) and the
+// download into `popResultsHere` — and, to bound how far it runs ahead, for the kernels of the push BEFORE this one.  The
+// kernels of this push are still running when pushData returns: the next push is prepared behind them.
+bool ClPipeline::pushChained(const std::vector<void*>& data, const std::vector<void*>& popResultsHere) {
+    const int S = (int)stages_.size();
+    const bool hasData = !data.empty(), hasPop = !popResultsHere.empty();
+    const int cur = counter & 1, prev = cur ^ 1;
+
+    for (int k = 0; k < S; k++) {
+        ClPipelineStage* s = stages_[k];
+        ck_handle q = s->cruncher_->numberCruncher()->worker(0).mainQueue();
+        ckQueueWaitEvent(q, s->inDone_[prev]);
+        ckQueueWaitEvent(q, k + 1 < S ? stages_[k + 1]->inDone_[prev] : s->outDone_[prev]);
+        s->cruncher_->setEnqueueMode(true);
+        s->run(false, mode_);
+        ckQueueRecordEvent(q, s->compDone_[cur]);
+    }
+    for (int k = 0; k < S; k++) {
+        ClPipelineStage* s = stages_[k];
+        if (k == 0 && hasData) {
+            ckQueueWaitEvent(s->forwardQueue_, s->compDone_[prev]);
+            for (size_t j = 0; j < s->inputs_.size() && j < data.size(); j++) {
+                ck_handle b = s->cruncher_->numberCruncher()->worker(0).buffer(s->inputs_[j]->bufDuplicate()->ref());
+                writeToBuffer(s->forwardQueue_, b, data[j]);
+            }
+            ckQueueRecordEvent(s->forwardQueue_, s->inDone_[cur]);
+        }
+        if (k + 1 < S) {
+            ClPipelineStage* nx = stages_[k + 1];
+            ckQueueWaitEvent(nx->forwardQueue_, s->compDone_[prev]);
+            ckQueueWaitEvent(nx->forwardQueue_, nx->compDone_[prev]);
+            for (size_t j = 0; j < s->outputs_.size() && j < nx->inputs_.size(); j++) {
+                ClArray* src = s->outputs_[j]->bufDuplicate();
+                ClArray* dst = nx->inputs_[j]->bufDuplicate();
+                const int64_t n = std::min(src->Length(), dst->Length());
+                ck_handle sb = s->cruncher_->numberCruncher()->worker(0).buffer(src->ref());
+                ck_handle db = nx->cruncher_->numberCruncher()->worker(0).buffer(dst->ref());
+                ckCopyBufferPeer(nx->forwardQueue_, db, sb, 0, (int32_t)n, nullptr, nullptr);  // NVLink, no host bounce
+            }
+            ckQueueRecordEvent(nx->forwardQueue_, nx->inDone_[cur]);
+        } else if (hasPop) {
+            // its own queue: the first stage's upload (same queue when S == 1) must not hold the download back
+            ckQueueWaitEvent(s->forwardQueue_, s->compDone_[prev]);
+            for (size_t j = 0; j < s->outputs_.size() && j < popResultsHere.size(); j++) {
+                ck_handle b = s->cruncher_->numberCruncher()->worker(0).buffer(s->outputs_[j]->bufDuplicate()->ref());
+                readFromBuffer(s->forwardQueue_, b, popResultsHere[j]);
+            }
+            ckQueueRecordEvent(s->forwardQueue_, s->outDone_[cur]);
+        }
+    }
+    // what the host itself must see, and a bound on its lead
+    if (hasData) finish(stages_[0]->forwardQueue_);
+    if (hasPop) finish(stages_[S - 1]->forwardQueue_);
+    for (auto* s : stages_) ckEventSynchronize(s->compDone_[prev]);
+
+    for (int i = 0; i < S; i++) {
+        if (hasData || i != 0)
+            for (auto& b : stages_[i]->inputs_) b->switchBuffers();
+        if (hasPop || i != S - 1)
+            for (auto& b : stages_[i]->outputs_) b->switchBuffers();
+    }
+    return finishPush(hasData, hasPop);
 }
 
 }  // namespace cekirdekler

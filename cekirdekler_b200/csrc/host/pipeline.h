@@ -83,12 +83,15 @@ class ClPipelineStage {  // ClPipeline.cs:146-1873
     std::string initMessage_;
     bool debug_;
     ck_handle forwardQueue_ = nullptr;  // a queue on this stage's device used for incoming hand-offs
+    // events of the chained (peer-to-peer) pushData, two deep (push p uses [p % 2], waits on [(p - 1) % 2]):
+    // this stage's kernels / the transfer that filled its input duplicates / the download that read its output duplicates
+    ck_handle compDone_[2] = {nullptr, nullptr}, inDone_[2] = {nullptr, nullptr}, outDone_[2] = {nullptr, nullptr};
     ck_handle forwardCtx_ = nullptr, forwardDev_ = nullptr, forwardPlat_ = nullptr;
 };
 
 class ClPipeline {  // ClPipeline.cs:41-139
   public:
-    ~ClPipeline() {}
+    ~ClPipeline();
     // data / popResultsHere: host arrays (one per input of the first stage / output of the last stage), or empty.
     // Returns true once the results delivered by this push are valid (ClPipeline.cs:114-124).
     bool pushData(const std::vector<void*>& data = {}, const std::vector<void*>& popResultsHere = {});
@@ -100,8 +103,11 @@ class ClPipeline {  // ClPipeline.cs:41-139
 
   private:
     friend class ClPipelineStage;
+    bool pushChained(const std::vector<void*>& data, const std::vector<void*>& popResultsHere);
+    bool finishPush(bool hasData, bool hasPop);
     std::vector<ClPipelineStage*> stages_;
     Forwarding mode_ = Forwarding::PeerToPeer;
+    bool chained_ = false;   // every stage on one device, peer-to-peer forwarding: pushes are ordered by events, not by a host join
 };
 
 }  // namespace cekirdekler
