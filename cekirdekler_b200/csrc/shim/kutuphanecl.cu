@@ -644,6 +644,12 @@ ck_handle createKernel(ck_handle hProgram, ck_handle hString) {
     }
     for (auto& kv : p->cubin->kernels)
         if (kv.first == k->name) k->nparams = kv.second;
+    // Load the kernel's code onto the device NOW.  CUDA loads a library kernel lazily at its first launch, and that load
+    // waits for the whole device; a first launch enqueued behind a user event that has not fired yet (ClUserEvent.cs:30-46:
+    // the host gates a queue, fills it, then triggers) would then wait for the gate inside cudaLaunchKernel and never return
+    // to the thread that is about to open it (seen on B200, round 2).  Asking for the attributes forces the load.
+    cudaFuncAttributes attr;
+    if (cudaFuncGetAttributes(&attr, (const void*)k->fn) != cudaSuccess) cudaGetLastError();
     return k;
 }
 void deleteKernel(ck_handle h) { del<Kernel>(h, Kind::Kernel); }
