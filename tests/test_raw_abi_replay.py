@@ -327,6 +327,32 @@ def test_host_array_helpers():
     w.dispose("random", seed=11, twice=True)
 
 
+def test_build_errors_come_back_as_a_code_and_a_log():
+    """ClProgram (ClProgram.cs:30-40, :64-101): a source that does not build gives a non-zero getProgramErr and a log the C#
+    reads as a string (and frees itself); kernels of such a program report an error instead of launching."""
+    w = RawWorker()
+    assert "warning" in w.build_log() or w.build_log() == "" or isinstance(w.build_log(), str)   # a good build: readable, maybe empty
+    src = L.writeToString(L.createString(), b"__kernel void broken(__global float* a) { a[0] = no_such_symbol; }")
+    bad = L.createProgram(w.ctx, w.dev, src)
+    L.deleteString(src)
+    assert L.getProgramErr(bad) != 0
+    p = L.readProgramErrString(bad)
+    try:
+        log = C.string_at(p).decode()
+    finally:
+        C.CDLL(None).free(C.c_void_p(p))
+    assert "no_such_symbol" in log
+    name = L.writeToString(L.createString(), b"broken")
+    k = L.createKernel(bad, name)
+    L.deleteString(name)
+    assert L.getKernelErr(k) != 0
+    off, glob, loc = w.rng(0), w.rng(N), w.rng(LOCAL)
+    assert L.compute(w.q, k, off, glob, loc) != 0
+    L.deleteKernel(k)
+    L.deleteProgram(bad)
+    w.dispose("forward")
+
+
 def test_workers_on_several_threads_with_deletes_in_any_order(gpus):
     """Parallel.For bodies (Cores.cs:671-824): one thread per worker, all calling the library at once, each worker then torn
     down in a different order, some of them twice (dispose() followed by the finalizer)."""
