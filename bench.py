@@ -366,10 +366,11 @@ def bench_image_kernels(ck, kernels, po, dev, pk, sets=6, rounds=3):
         a.view[:] = frame
         S.append((a, b, c, h, acc))
     gs, ls = kernels.strip_launch(Wf, Hf, RB)
+    hg = int(os.environ.get("CK_HIST_GROUPS", "592"))       # work-groups of histogramStrips (experiment hook)
     # name: (kernel names, argument group, compute id, global range, local, elements per item of each argument, algorithmic bytes)
     calls = {"blurStrips": ("blurStrips", lambda s: s[0].nextParam(s[1], dims), 11, gs, ls, [1, 1, 1], 8.0 * n),
              "sobelStrips": ("sobelStrips", lambda s: s[1].nextParam(s[2], dims), 12, gs, ls, [1, 1, 1], 8.0 * n),
-             "histogramStrips": ("histogramStrips", lambda s: s[2].nextParam(s[3], dims, s[4]), 13, 592 * 256, 256, [1, 1, 1, 1], 4.0 * n + 1024),
+             "histogramStrips": ("histogramStrips", lambda s: s[2].nextParam(s[3], dims, s[4]), 13, hg * 256, 256, [1, 1, 1, 1], 4.0 * n + 1024),
              "blurSobelHistogram": ("blurSobelHistogram", lambda s: s[0].nextParam(s[3], dims, s[4]), 14, gs, ls, [1, 1, 1, 1], 4.0 * n + 1024),
              "gaussianBlur": ("gaussianBlur", lambda s: s[0].nextParam(s[1], dims), 1, n, 256, [1, 1, 1], 8.0 * n),
              "gaussianBlur8": ("gaussianBlur8", lambda s: s[0].nextParam(s[1], dims), 4, n // 8, 256, [1, 8, 1], 8.0 * n),
@@ -465,6 +466,20 @@ def bench_c1(ck, kernels, po, dev, pk, sms, reps=200):
     rw = ["", ""]
     run("resident_kernel_only", lambda: g.compute(cr, 3, MK, npx // E, 256, 0, False, True, 4, readWritesReady=rw,
                                                   elementsPerItemReady=[1, E]), 3)
+    # the host side alone: enqueue mode (no wait per call) on one work-group, so that the GPU is never what is waited for
+    cr.enqueueMode = True
+    tiny = lambda: g.compute(cr, 4, MK, 256, 256, 0, False, True, 4, readWritesReady=rw, elementsPerItemReady=[1, E])
+    for _ in range(200):
+        assert tiny() == 0
+    cr.enqueueMode = False
+    cr.enqueueMode = True
+    t0 = time.perf_counter()
+    for _ in range(5000):
+        tiny()
+    dt_host = (time.perf_counter() - t0) / 5000
+    cr.enqueueMode = False
+    res["host_us_per_call_enqueue_mode"] = {"us": dt_host * 1e6, "note": "compute() through the Python binding and the C++ layer down to "
+                                            "cudaLaunchKernel, no wait: 5000 calls of one work-group in enqueue mode"}
     k = res["resident_kernel_only"]["us_per_call_device_span"] * 1e-6
     peak = 2.0 * 128 * sms * pk["sm_max_mhz"] * 1e6 / 1e12
     ach = 8.0 * res["iterations_total"] / k / 1e12
