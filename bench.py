@@ -649,7 +649,7 @@ def bench_nbody(ck, kernels, po, devs, pk, sms, steps, warmup, spmd_attach=None,
            "GInter_per_s": inter / dt_dev / 1e9, "GInter_per_s_e2e": inter / dt_wall / 1e9, "scratch_MB": kfloats * 4096 / 1e6,
            "parity": parity,
            "roofline": {"bound": "fp32", "achieved": ach, "peak": peak, "unit": "TFLOP/s", "frac": ach / peak,
-                        "traffic": ncu_traffic("nbody") if n_gpus == 1 else None,
+                        "traffic": ncu_traffic("nbody", "r2_ncu_summary.json") if n_gpus == 1 else None,
                         "note": "20 FLOP per interaction over the kernel's own launch time (arrays resident); GInter_per_s "
                                 "adds the 2 MiB position upload and the slice transfers, GInter_per_s_e2e the whole host call"}}
     def finish():
