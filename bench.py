@@ -586,6 +586,8 @@ def bench_nbody(ck, kernels, po, devs, pk, sms, steps, warmup, spmd_attach=None,
     nb_src = kernels.source("nbody")
     if os.environ.get("CK_NBW_TPW"):        # experiment hook: j tiles per warp and unit (profiles/r2_nbody_unit_size.md)
         nb_src = f"// ck-nvrtc: -DNBW_TILES_PER_WARP={int(os.environ['CK_NBW_TPW'])}\n" + nb_src
+    if os.environ.get("CK_NBW_LB"):         # experiment hook: "<max threads> <min groups per SM>" for nBody3Dw / nBody3Dwp
+        nb_src = "".join(f"// ck-launch-bounds: {k} {os.environ['CK_NBW_LB']}\n" for k in ("nBody3Dw", "nBody3Dwp")) + nb_src
     cr = ck.ClNumberCruncher(devs, nb_src)
     assert cr.errorCode() == 0, cr.errorMessage()
     cr.balancerMode = 2
