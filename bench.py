@@ -48,6 +48,7 @@ METRIC = "mandelbrot_mpix_per_s"
 UNIT = "Mpix/s"
 W = H = 16384
 MAX_ITER = 4096
+WORKLOAD = f"mandelbrot {W}x{H} maxIter {MAX_ITER} view [-2,1]x[-1.5,1.5] (BASELINE configs[2])"   # the same string in both arms
 E = 1  # pixels per work-item: 1 for `mandelbrot1` (the default), 4 for `mandelbrot`; set from --mandel-kernel in main()
 MK = "mandelbrot1"
 
@@ -171,7 +172,7 @@ def run_reference(args):
         "impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": tot_s / args.steps * 1e3, "higher_is_better": True, "scaling": "strong",
         "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": f"mandelbrot {W}x{H} maxIter {MAX_ITER} view [-2,1]x[-1.5,1.5] (BASELINE configs[2])",
+        "config": {"workload": WORKLOAD,
                    "note": "the reference's PoCL/C# path cannot run on this box (no CLR, no OpenCL); this is the CPU "
                            "restatement oracle/oracle.cpp on all host threads"},
         "cpu_baseline": {"value": v, "unit": UNIT, "cores": po.threads(), "kind": "port",
@@ -950,8 +951,8 @@ def run_ours(args):
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": n_gpus, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
             "dtype": "f32", "data": "synthetic",
-            "config": {"workload": f"mandelbrot {W}x{H} maxIter {MAX_ITER} view [-2,1]x[-1.5,1.5] (BASELINE configs[2]), "
-                                   f"kernel {MK}, {E} pixel(s) per work-item, local 256, via ClNumberCruncher.compute",
+            "config": {"workload": WORKLOAD,
+                       "kernel": f"{MK}, {E} pixel(s) per work-item, local 256, via ClNumberCruncher.compute",
                        "parallelism": ("spmd one process per GPU" if spmd_mode else "one process") + f" x{n_gpus}",
                        "l2": "output 1 GiB per step >> 126 MB L2, no reuse between steps",
                        "balancer": args.balancer, "smooth_load_balancer": not args.no_smooth, "balancer_settle_steps": settle, "host_memory_policy_rank0": numa},
