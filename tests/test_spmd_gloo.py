@@ -75,3 +75,32 @@ def test_two_ranks_agree_on_the_split(mode):
     assert abs(last[1] / last[0] - 2.5) < 0.15                  # converged to the speed ratio
     # from the second call on, both ranks saw both times
     assert all(t > 0 for t in a[2]["times"])
+
+
+def test_shared_memory_slots_exchange_many_calls_between_threads(tmp_path):
+    """spmd._SharedSlots on its own (no process group): three "ranks" on three threads exchange 200 values; every rank
+    must see, at every call, exactly the values the others posted for THAT call (two banks are enough: nobody can be more
+    than one call ahead of the slowest reader)."""
+    import threading
+
+    from cekirdekler_b200.spmd import _SharedSlots
+
+    world, calls = 3, 200      # threads share the GIL, so every hand-over costs a switch interval; ranks are processes
+    path = str(tmp_path / "slots")
+    slots = [_SharedSlots(0, world, path, create=True)] + [_SharedSlots(r, world, path, create=False) for r in range(1, world)]
+    seen = [[] for _ in range(world)]
+
+    def body(r):
+        for k in range(calls):
+            seen[r].append(slots[r].exchange(1000.0 * k + r, timeout_s=60.0))
+
+    threads = [threading.Thread(target=body, args=(r,)) for r in range(world)]
+    for t in threads:
+        t.start()
+    for t in threads:
+        t.join()
+    for r in range(world):
+        assert len(seen[r]) == calls
+        for k in (0, 1, 2, 77, calls - 1):
+            assert seen[r][k] == [1000.0 * k + q for q in range(world)]
+    assert all(seen[0][k] == seen[1][k] == seen[2][k] for k in range(calls))
