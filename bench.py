@@ -871,6 +871,22 @@ def run_ours(args):
         local_iters += int(out.view[p0:p0 + cnt].sum(dtype=np.int64))
     total_iters = allsum(float(local_iters))
     line_cpu, parity = None, None
+    # every rank checks its OWN slice of the image against the oracle on a stride-257 sample (the ranks' shares differ, and
+    # rank 0's larger sample below only sees rank 0's); mismatches and pixel counts are summed over the ranks
+    own_checked, own_bad = 0, 0
+    if spmd_mode:
+        po.lib().oracle_set_threads(max(1, po.threads() // max(1, world)))   # the ranks share the host's cores here
+        for (p0, cnt) in my_slices(CID_E2E):
+            m = (cnt - 17) // 257
+            if m <= 0:
+                continue
+            ref = np.zeros(m, np.int32)
+            po.mandelbrot_sample(view.view, p0 + 17, 257, m, ref)
+            got = out.view[p0 + 17:p0 + 17 + 257 * m:257]
+            own_checked += m
+            own_bad += int((got != ref).sum())
+        po.use_all_cores()
+    all_checked, all_bad = int(allsum(float(own_checked))), int(allsum(float(own_bad)))
     if rank == 0:
         s = cpu_sample(po, view.view, 12.0)
         idx = s["offset"] + s["stride"] * np.arange(s["pixels"], dtype=np.int64)
@@ -879,6 +895,8 @@ def run_ours(args):
             mine[p0:p0 + cnt] = True
         sel = mine[idx]
         parity = {"sample_pixels_checked": int(sel.sum()), "mismatches": int((out.view[idx[sel]] != s["values"][sel]).sum())}
+        if spmd_mode:
+            parity["every_rank_own_slice"] = {"sample_pixels_checked": all_checked, "mismatches": all_bad, "stride": 257}
         line_cpu = {"value": s["pixels"] / s["seconds"] / 1e6, "unit": UNIT, "cores": po.threads(), "kind": "port",
                     "sample": f"{s['pixels']} pixels (odd stride {s['stride']} across the whole {W}x{H} image), {s['iters']} iterations, {s['seconds']:.1f} s"}
 
