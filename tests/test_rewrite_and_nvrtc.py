@@ -148,3 +148,19 @@ def test_device_side_enqueue_is_refused_with_a_clear_message():
     rc, log, nbytes = compile_check(src)
     assert rc != 0 and nbytes == 0
     assert "enqueue_kernel" in log and "not supported" in log
+
+
+def test_component_selection_rewrite_on_postfix_expressions():
+    """What the source rewrite does with `.xy .zw .lo .hi .xyz .s0-.s3`: the whole postfix expression in front is wrapped,
+    numbers and comments are left alone."""
+    from cekirdekler_b200 import kernels
+
+    def body(src):
+        return kernels.rewritten_with_prelude(src).split('#line 1 "user_kernels.cu"\n', 1)[1]
+
+    out = body("void f(float4 a, float4* p, S* q) { float2 r = a.xy; r = p[3].zw; r = q->v.lo; r = g(a, 1).hi; float3 t = (a + a).xyz; "
+               "float s = a.s2 + 1.5f + 2.f; /* a.xy stays */ }")
+    assert "ck_xy(a)" in out and "ck_zw(p[3])" in out and "ck_lo(q->v)" in out and "ck_hi(g(a, 1))" in out and "ck_xyz((a + a))" in out
+    assert "a.z + 1.5f + 2.f" in out and "/* a.xy stays */" in out
+    assert body("int hi = lo.hi;") == "int hi = ck_hi(lo);"           # names called lo / hi are ordinary identifiers
+    assert body("x = v2.xy;") == "x = ck_xy(v2);"                     # an identifier that ends in a digit is not a number
