@@ -51,6 +51,7 @@ MAX_ITER = 4096
 WORKLOAD = f"mandelbrot {W}x{H} maxIter {MAX_ITER} view [-2,1]x[-1.5,1.5] (BASELINE configs[2])"   # the same string in both arms
 E = 1  # pixels per work-item: 1 for `mandelbrot1` (the default), 4 for `mandelbrot`; set from --mandel-kernel in main()
 MK = "mandelbrot1"
+LOCAL = int(os.environ.get("CK_MANDEL_LOCAL", "256"))   # work-group size of the headline kernel (experiment hook; one B200: 64 -> 84.7 %, 128 and 256 -> 86.7 %, 512 -> 85.8 %, 1024 -> 84.8 % of FP32)
 
 
 def peaks():
@@ -798,7 +799,7 @@ def run_ours(args):
     shares, imbalance = [], []
 
     def step_resident():
-        assert g.compute(cr, CID_RES, MK, items, 256, 0, False, True, 4, readWritesReady=rw_res, elementsPerItemReady=[1, E]) == 0
+        assert g.compute(cr, CID_RES, MK, items, LOCAL, 0, False, True, 4, readWritesReady=rw_res, elementsPerItemReady=[1, E]) == 0
         t_local = cr.benchmarks(CID_RES)
         return t_local
 
@@ -848,7 +849,7 @@ def run_ours(args):
     def step_e2e():
         barrier()
         t0 = time.perf_counter()
-        assert g.compute(cr, CID_E2E, MK, items, 256, 0, True, args.e2e_mode == "event", args.e2e_blobs) == 0
+        assert g.compute(cr, CID_E2E, MK, items, LOCAL, 0, True, args.e2e_mode == "event", args.e2e_blobs) == 0
         dt = allmax(time.perf_counter() - t0)
         tt = cr_times(cr, CID_E2E, cr.benchmarks(CID_E2E), spmd_mode,
                       allgather=(lambda v: gather(dist, torch, torch_dev, v, world)) if spmd_mode else None)
@@ -970,7 +971,7 @@ def run_ours(args):
             "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
             "dtype": "f32", "data": "synthetic",
             "config": {"workload": WORKLOAD,
-                       "kernel": f"{MK}, {E} pixel(s) per work-item, local 256, via ClNumberCruncher.compute",
+                       "kernel": f"{MK}, {E} pixel(s) per work-item, local {LOCAL}, via ClNumberCruncher.compute",
                        "parallelism": ("spmd one process per GPU" if spmd_mode else "one process") + f" x{n_gpus}",
                        "l2": "output 1 GiB per step >> 126 MB L2, no reuse between steps",
                        "balancer": args.balancer, "smooth_load_balancer": not args.no_smooth, "balancer_settle_steps": settle, "host_memory_policy_rank0": numa},
