@@ -331,7 +331,7 @@ def test_build_errors_come_back_as_a_code_and_a_log():
     """ClProgram (ClProgram.cs:30-40, :64-101): a source that does not build gives a non-zero getProgramErr and a log the C#
     reads as a string (and frees itself); kernels of such a program report an error instead of launching."""
     w = RawWorker()
-    assert "warning" in w.build_log() or w.build_log() == "" or isinstance(w.build_log(), str)   # a good build: readable, maybe empty
+    assert "error" not in w.build_log()                  # a good build: the log is readable (and usually empty)
     src = L.writeToString(L.createString(), b"__kernel void broken(__global float* a) { a[0] = no_such_symbol; }")
     bad = L.createProgram(w.ctx, w.dev, src)
     L.deleteString(src)
